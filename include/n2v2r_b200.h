@@ -1,0 +1,210 @@
+/*
+ * n2v2r_b200.h -- C ABI of the B200-native UASE embed-and-rank hot path.
+ *
+ * Drop-in boundary for pmandros/node2vec2rank's hot path.  The
+ * reference has no FFI of its own (pure Python); each entry point below replaces the
+ * Python function cited next to it.  A maintainer binds these with ctypes (see
+ * INTEGRATION.md); node2vec2rank_b200/_native.py is that binding.
+ *
+ * Conventions
+ *   - every pointer named d_* is DEVICE memory owned by the caller; h_* is HOST memory;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = default stream);
+ *   - all functions return n2v2r_status_t; n2v2r_last_error() gives the message of the
+ *     last failure on the calling thread;
+ *   - no function allocates device memory behind the caller's back: scratch space is
+ *     passed as (d_ws, ws_bytes) and sized with the matching *_workspace_bytes call;
+ *   - functions are asynchronous on `stream` unless a host scalar must be returned
+ *     (select_nonzero, uase, planes_needed, is_symmetric), which synchronise the stream.
+ *
+ * Storage of a graph layer ("planes"): the (rows x cols) matrix is held as P in {1,2,3}
+ * bf16 planes, value = plane0 + plane1 + plane2, each plane row-major with leading
+ * dimension ld (elements, multiple of 64, padding zero-filled).  P=1 is exact for
+ * binarised layers (and any bf16-representable weights), P=2 keeps 16 mantissa bits,
+ * P=3 is exact fp32.
+ */
+#ifndef N2V2R_B200_H
+#define N2V2R_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define N2V2R_ABI_VERSION 1
+
+typedef enum {
+  N2V2R_OK = 0,
+  N2V2R_EINVAL = 1,        /* bad argument                                            */
+  N2V2R_ENOMEM = 2,        /* workspace too small                                     */
+  N2V2R_ECUDA = 3,         /* CUDA runtime / driver error                             */
+  N2V2R_ECOMM = 4,         /* all-reduce callback failed                              */
+  N2V2R_ENOTCONV = 5,      /* solver hit max_iters before tol (results still written) */
+  N2V2R_EUNSUPPORTED = 6   /* device is not sm_100 / shape outside kernel limits      */
+} n2v2r_status_t;
+
+typedef enum { N2V2R_F32 = 0, N2V2R_F64 = 1 } n2v2r_dtype_t;
+typedef enum { N2V2R_EUCLIDEAN = 0, N2V2R_COSINE = 1, N2V2R_CORRELATION = 2 } n2v2r_metric_t;
+typedef enum { N2V2R_SEQUENTIAL = 0, N2V2R_ONE_VS_BEFORE = 1, N2V2R_ONE_VS_REST = 2 } n2v2r_strategy_t;
+typedef enum { N2V2R_ALGO_TCGEN05 = 0, N2V2R_ALGO_SIMT = 1 } n2v2r_algo_t;
+
+int n2v2r_abi_version(void);
+const char* n2v2r_last_error(void);
+/* sm count, compute capability (major*10+minor) and total memory of `device`. */
+int n2v2r_device_info(int device, int* sm_count, int* cc, size_t* total_mem);
+
+/* ------------------------------------------------------------------------------------
+ * K0  synthetic stochastic block model layer (benchmark input).
+ * Counter-based: entry (i,j), i<j, of layer `layer` is a pure function of
+ * (seed, layer, i, j); A[j,i] = A[i,j]; zero diagonal.  community(i) = i % K.
+ * h_B is the K*K row-major (symmetric) block probability matrix on the HOST.
+ * weighted=0: A in {0,1}; weighted=1: A = edge * w, w in (0,1] a second counter draw.
+ * NumPy twin: node2vec2rank_b200/synthetic.py (bit-identical).
+ * ---------------------------------------------------------------------------------- */
+int n2v2r_sbm_generate(void* stream, float* d_out, int64_t n, int64_t ld, int K,
+                       const float* h_B, uint64_t seed, int layer, int weighted);
+
+/* ------------------------------------------------------------------------------------
+ * K1a  order statistics for the percentile cut.
+ * Replaces np.percentile(x[x.nonzero()], q) at preprocessing_utils.py:134.
+ * Considers y = transform(x) (abs if `absolute`, then y < thr -> 0 if has_thr) and only
+ * y != 0.  Returns the number of nonzeros and, for position pos = frac*(nnz-1) (evaluated in
+ * float32 when index_f32 != 0, as NumPy does for float32 data; returned in *h_pos), the two
+ * adjacent order statistics y_(floor(pos)) and y_(floor(pos)+1) (ascending, 0-based),
+ * exactly (multi-pass radix select on the order-preserving bit pattern).  The caller does
+ * the linear interpolation in the input dtype like NumPy does.  Synchronises `stream`.
+ * ---------------------------------------------------------------------------------- */
+size_t n2v2r_select_workspace_bytes(void);
+int n2v2r_select_nonzero(void* stream, const void* d_in, int dtype, int64_t rows, int64_t cols,
+                         int64_t ld, int absolute, int has_thr, double thr, double frac, int index_f32,
+                         void* d_ws, size_t ws_bytes,
+                         int64_t* h_nnz, double* h_lo, double* h_hi, double* h_pos);
+
+/* ------------------------------------------------------------------------------------
+ * K1b  fused load pass.  Replaces preprocessing_utils.py:124-141 (abs -> threshold ->
+ * percentile cut -> binarize -> fp32) and, as a by-product, the column sums that
+ * model.py:293-294 (degree_difference_ranking) needs.
+ * Any of d_out_f32 / d_planes / d_colsum may be NULL.  d_planes holds n_planes planes of
+ * rows*ld_p bf16 each (plane stride rows*ld_p); padding columns [cols, ld_p) are zeroed.
+ * d_colsum (cols doubles) must be zeroed by the caller; sums are of the fp32 output values.
+ * ---------------------------------------------------------------------------------- */
+int n2v2r_transform(void* stream, const void* d_in, int dtype, int64_t rows, int64_t cols, int64_t ld_in,
+                    int absolute, int has_thr, double thr, int has_cut, double cut, int binarize,
+                    float* d_out_f32, int64_t ld_out,
+                    void* d_planes, int n_planes, int64_t ld_p,
+                    double* d_colsum);
+
+/* Minimum number of bf16 planes (1..3) that represents every entry of the fp32 matrix
+ * exactly.  Synchronises `stream`. */
+int n2v2r_planes_needed(void* stream, const float* d_in, int64_t rows, int64_t cols, int64_t ld,
+                        int* h_planes);
+/* 1 if the square plane set is symmetric.  Synchronises `stream`. */
+int n2v2r_is_symmetric(void* stream, const void* d_planes, int n_planes, int64_t n, int64_t ld_p,
+                       int* h_symmetric);
+/* out = in^T for every plane (used only for non-symmetric layers). */
+int n2v2r_transpose_planes(void* stream, const void* d_planes, int n_planes, int64_t n, int64_t ld_p,
+                           void* d_out);
+
+/* ------------------------------------------------------------------------------------
+ * K2  bipartite -> unipartite projection on the tensor cores.
+ * Replaces bipartite_to_unipartite_projection (preprocessing_utils.py:16-32):
+ * on_rows=0: out = W^T W (cols x cols); on_rows=1: out = W W^T (rows x rows).
+ * W is (rows x cols) row-major, dtype F32 or F64; operands are split into three bf16
+ * terms (24 mantissa bits) and accumulated in fp32 (tcgen05.mma, TMA-fed).
+ * ---------------------------------------------------------------------------------- */
+size_t n2v2r_project_workspace_bytes(int64_t rows, int64_t cols, int on_rows);
+int n2v2r_project(void* stream, const void* d_W, int dtype, int64_t rows, int64_t cols, int64_t ld,
+                  int on_rows, float* d_out, int64_t ld_out, void* d_ws, size_t ws_bytes);
+
+/* ------------------------------------------------------------------------------------
+ * K3-K8  UASE: truncated SVD of the unfolded matrix [A_1 | ... | A_T] and the per-layer
+ * right embeddings V_t * S^(1/2).  Replaces spectral_embedding.UASE as called at
+ * model.py:54-55 (scipy svds / ARPACK underneath).
+ * Randomised block subspace iteration with Rayleigh-Ritz and optional Chebyshev filter;
+ * CholeskyQR2; single-CTA Jacobi for the l x l eigenproblem; the only O(n^2) work is the
+ * streaming skinny products Y += A_t X and Z_t = A_t^T Q.
+ * Layer sharding: this process owns T_local layers [layer_offset, layer_offset+T_local)
+ * of T_global; `allreduce` (may be NULL when T_local == T_global) sums a device buffer
+ * over all processes, in place, ordered on `stream`.
+ * ---------------------------------------------------------------------------------- */
+typedef struct {
+  const void* d_planes;    /* n_planes planes, each n x ld bf16                         */
+  const void* d_planes_t;  /* planes of A^T, or NULL when the layer is symmetric         */
+  int32_t n_planes;
+  int32_t reserved;
+  int64_t ld;
+} n2v2r_layer_t;
+
+typedef struct {
+  int64_t n;               /* nodes                                                      */
+  int32_t T_local, T_global, layer_offset;
+  int32_t k;               /* embedding dimension (max of the sweep), k <= l             */
+  int32_t l;               /* block width: 16, 32, 48, 64 or 80                          */
+  int32_t max_iters;       /* cap on operator applications (A A^T)                       */
+  int32_t min_iters;
+  int32_t cheb_degree;     /* 1 = plain subspace iteration; m>1 = degree-m Chebyshev filter */
+  int32_t algo;            /* n2v2r_algo_t                                               */
+  int32_t k_chunk;         /* columns of A per accumulation unit (0 = default)           */
+  int32_t n_check;         /* number of entries of h_check_dims                          */
+  double tol;              /* stop when the subspace-angle bound at every checked d <= tol */
+  uint64_t seed;
+  const int32_t* h_check_dims; /* swept dimensions d (gap-aware stopping rule); may be NULL */
+} n2v2r_uase_params_t;
+
+typedef struct {
+  int32_t iterations;      /* operator applications done                                 */
+  int32_t layer_passes;    /* number of (layer x skinny product) launches                */
+  int32_t converged;
+  int32_t kernel_launches;
+  double stream_ms;        /* CUDA-event time spent in the streaming kernels             */
+  double total_ms;
+  double stream_bytes;     /* algorithmic bytes of those launches            */
+  double max_angle_bound;  /* final value of the stopping quantity                       */
+  double resid[96];        /* final relative residual per Ritz pair                      */
+  double ritz[96];         /* Ritz values (sigma^2), descending                          */
+} n2v2r_uase_stats_t;
+
+typedef int (*n2v2r_allreduce_fn)(void* user, void* d_buf, int64_t count, int dtype, void* stream);
+
+size_t n2v2r_uase_workspace_bytes(const n2v2r_uase_params_t* p);
+int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2r_layer_t* h_layers,
+               void* d_ws, size_t ws_bytes, n2v2r_allreduce_fn allreduce, void* user,
+               float* d_embed /* T_local x n x k */, float* d_left /* n x k or NULL */,
+               double* h_sigma /* k */, n2v2r_uase_stats_t* h_stats);
+
+/* One streaming skinny product, exposed for tests / roofline measurement:
+ * d_out (n x l fp32) = A X  (transpose=0) or A^T X (transpose=1), X = d_x (n x l fp32). */
+size_t n2v2r_apply_workspace_bytes(int64_t n, int l, int k_chunk);
+int n2v2r_layer_apply(void* stream, const n2v2r_layer_t* h_layer, int64_t n, int l, int transpose,
+                      const float* d_x, float* d_out, int algo, int k_chunk,
+                      void* d_ws, size_t ws_bytes);
+
+/* ------------------------------------------------------------------------------------
+ * K9  per-node distances for every swept d.  Replaces N2V2R.__rank (model.py:57-96) +
+ * compute_pairwise_distances (model_utils.py:39-67).
+ * d_embed: (T x n x k) fp32.  Column c uses the leading h_col_dim[c] components and metric
+ * h_col_metric[c].  Comparisons follow `strategy`: sequential / one_vs_before give
+ * T-1 comparisons (layers 1..T-1), one_vs_rest gives T.  float64 arithmetic.
+ * d_scores: (n_comparisons x n_cols x n) doubles, each column contiguous.
+ * ---------------------------------------------------------------------------------- */
+int n2v2r_distances(void* stream, const float* d_embed, int T, int64_t n, int k,
+                    const int32_t* h_col_dim, const int32_t* h_col_metric, int n_cols,
+                    int strategy, double* d_scores);
+
+/* ------------------------------------------------------------------------------------
+ * K10+K11  descending rank of every score column (segmented radix sort on the
+ * order-preserving 64-bit pattern; ties stable by node position; NaN last) and Borda
+ * points sum_c (n - position_c).  Replaces aggregate_transform (model.py:167-185) +
+ * borda_aggregate_parallel/_get_ranking (model_utils.py:22-36).
+ * d_scores: (n_cols x n) doubles; d_positions: (n_cols x n) int32 or NULL;
+ * d_borda: n int64.
+ * ---------------------------------------------------------------------------------- */
+size_t n2v2r_rank_workspace_bytes(int64_t n, int n_cols);
+int n2v2r_rank_borda(void* stream, const double* d_scores, int64_t n, int n_cols,
+                     int32_t* d_positions, int64_t* d_borda, void* d_ws, size_t ws_bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* N2V2R_B200_H */

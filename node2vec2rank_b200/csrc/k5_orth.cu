@@ -1,0 +1,463 @@
+// K5-K8: Gram / Rayleigh-Ritz reductions, single-CTA Jacobi + Cholesky, small applies.
+// Replaces np.linalg.qr (_svds.py:508) and the dense svd of the projected matrix
+// (_svds.py:518) inside scipy svds as reached from model.py:54-55.
+#include "k5_orth.cuh"
+#include <math.h>
+
+namespace n2v2r {
+
+// ---- X^T Y partials: each CTA reduces a slab of rows into an l x l fp64 block ------------
+// 256 threads; thread owns entries e = tid, tid+256, ... of the l*l output.
+__global__ void __launch_bounds__(256) xty_kernel(const float* __restrict__ X, const float* __restrict__ Y, int64_t n, int l,
+                                                  int rows_per_cta, double* __restrict__ partials) {
+  extern __shared__ float sm[];             // 2 * 32 * l
+  float* sx = sm;
+  float* sy = sm + 32 * l;
+  const int64_t r0 = (int64_t)blockIdx.x * rows_per_cta;
+  const int64_t r1 = (r0 + rows_per_cta < n) ? r0 + rows_per_cta : n;
+  const int ll = l * l;
+  double acc[25];                           // ceil(80*80/256) = 25
+#pragma unroll
+  for (int q = 0; q < 25; ++q) acc[q] = 0.0;
+  for (int64_t rb = r0; rb < r1; rb += 32) {
+    const int rows = (int)((r1 - rb < 32) ? (r1 - rb) : 32);
+    for (int t = threadIdx.x; t < 32 * l; t += 256) {
+      const int r = t / l;
+      sx[t] = r < rows ? X[(rb + r) * l + (t - r * l)] : 0.f;
+      sy[t] = r < rows ? Y[(rb + r) * l + (t - r * l)] : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < 25; ++q) {
+      const int e = threadIdx.x + q * 256;
+      if (e < ll) {
+        const int a = e / l, b = e - a * l;
+        double s = 0.0;
+#pragma unroll 8
+        for (int r = 0; r < 32; ++r) s += (double)sx[r * l + a] * (double)sy[r * l + b];
+        acc[q] += s;
+      }
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int q = 0; q < 25; ++q) {
+    const int e = threadIdx.x + q * 256;
+    if (e < ll) partials[(size_t)blockIdx.x * ll + e] = acc[q];
+  }
+}
+
+// fixed-order sum of the per-CTA partials (deterministic)
+__global__ void sum_partials_kernel(const double* __restrict__ partials, int n_parts, int count, double* __restrict__ out,
+                                    int accumulate) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= count) return;
+  double s = accumulate ? out[e] : 0.0;
+  for (int p = 0; p < n_parts; ++p) s += partials[(size_t)p * count + e];
+  out[e] = s;
+}
+
+// ---- single-CTA dense helpers on l x l fp64 matrices in shared memory ----------------------
+__device__ void jacobi_eig(double* A, double* V, int l, double* cs, int* pq, double* red) {
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const int half = l / 2;
+  for (int e = tid; e < l * l; e += nt) V[e] = ((e / l) == (e % l)) ? 1.0 : 0.0;
+  __syncthreads();
+  for (int sweep = 0; sweep < 40; ++sweep) {
+    // off-diagonal and total norms
+    double off = 0.0, tot = 0.0;
+    for (int e = tid; e < l * l; e += nt) {
+      const double v = A[e] * A[e];
+      tot += v;
+      if ((e / l) != (e % l)) off += v;
+    }
+    off = warp_sum(off); tot = warp_sum(tot);
+    if ((tid & 31) == 0) { red[(tid >> 5) * 2] = off; red[(tid >> 5) * 2 + 1] = tot; }
+    __syncthreads();
+    off = 0.0; tot = 0.0;
+    for (int w = 0; w < (nt >> 5); ++w) { off += red[w * 2]; tot += red[w * 2 + 1]; }
+    __syncthreads();
+    if (off <= 1e-30 * tot || tot == 0.0) break;
+    for (int r = 0; r < l - 1; ++r) {
+      if (tid < half) {
+        int p, q;
+        if (tid == 0) { p = l - 1; q = r; }
+        else { p = (r + tid) % (l - 1); q = (r - tid + (l - 1)) % (l - 1); }
+        if (p > q) { const int t = p; p = q; q = t; }
+        const double apq = A[p * l + q], app = A[p * l + p], aqq = A[q * l + q];
+        double c = 1.0, s = 0.0;
+        if (fabs(apq) > 1e-300 && fabs(apq) > 1e-18 * sqrt(fabs(app * aqq)) ) {
+          const double theta = (aqq - app) / (2.0 * apq);
+          const double t = (theta >= 0.0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
+          c = 1.0 / sqrt(t * t + 1.0);
+          s = t * c;
+        }
+        cs[2 * tid] = c; cs[2 * tid + 1] = s; pq[2 * tid] = p; pq[2 * tid + 1] = q;
+      }
+      __syncthreads();
+      // columns: A <- A J, V <- V J
+      for (int e = tid; e < l * half; e += nt) {
+        const int k = e / half, i = e - k * half;
+        const int p = pq[2 * i], q = pq[2 * i + 1];
+        const double c = cs[2 * i], s = cs[2 * i + 1];
+        const double akp = A[k * l + p], akq = A[k * l + q];
+        A[k * l + p] = c * akp - s * akq;
+        A[k * l + q] = s * akp + c * akq;
+        const double vkp = V[k * l + p], vkq = V[k * l + q];
+        V[k * l + p] = c * vkp - s * vkq;
+        V[k * l + q] = s * vkp + c * vkq;
+      }
+      __syncthreads();
+      // rows: A <- J^T A
+      for (int e = tid; e < l * half; e += nt) {
+        const int i = e / l, k = e - i * l;
+        const int p = pq[2 * i], q = pq[2 * i + 1];
+        const double c = cs[2 * i], s = cs[2 * i + 1];
+        const double apk = A[p * l + k], aqk = A[q * l + k];
+        A[p * l + k] = c * apk - s * aqk;
+        A[q * l + k] = s * apk + c * aqk;
+      }
+      __syncthreads();
+    }
+  }
+}
+
+// sort eigenpairs descending: lam_out[rank] , W[:, rank] = V[:, i]
+__device__ void sort_eig_desc(const double* A, const double* V, int l, double* lam, double* W) {
+  const int tid = threadIdx.x, nt = blockDim.x;
+  for (int i = tid; i < l; i += nt) {
+    const double li = A[i * l + i];
+    int rank = 0;
+    for (int j = 0; j < l; ++j) {
+      const double lj = A[j * l + j];
+      rank += (lj > li) || (lj == li && j < i);
+    }
+    lam[rank] = li;
+    for (int k = 0; k < l; ++k) W[k * l + rank] = V[k * l + i];
+  }
+  __syncthreads();
+}
+
+// C = A * B (l x l), all in shared memory
+__device__ void matmul_ll(const double* A, const double* B, double* C, int l, bool transA) {
+  for (int e = threadIdx.x; e < l * l; e += blockDim.x) {
+    const int i = e / l, j = e - i * l;
+    double s = 0.0;
+    for (int k = 0; k < l; ++k) s += (transA ? A[k * l + i] : A[i * l + k]) * B[k * l + j];
+    C[e] = s;
+  }
+  __syncthreads();
+}
+
+// In-place upper Cholesky M = R^T R; returns false on breakdown (pivot <= eps * max diag).
+__device__ bool cholesky_upper(double* M, int l, int* flag) {
+  const int tid = threadIdx.x, nt = blockDim.x;
+  double dmax = 0.0;
+  for (int i = 0; i < l; ++i) dmax = fmax(dmax, M[i * l + i]);
+  if (tid == 0) *flag = 0;
+  __syncthreads();
+  for (int j = 0; j < l; ++j) {
+    const double piv = M[j * l + j];
+    if (!(piv > 1e-13 * dmax)) { if (tid == 0) *flag = 1; __syncthreads(); return false; }
+    __syncthreads();
+    const double d = sqrt(piv);
+    for (int k = j + tid; k < l; k += nt) M[j * l + k] = M[j * l + k] / d;   // row j of R
+    __syncthreads();
+    for (int e = tid; e < (l - j - 1) * (l - j - 1); e += nt) {
+      const int a = j + 1 + e / (l - j - 1), b = j + 1 + e % (l - j - 1);
+      if (b >= a) M[a * l + b] -= M[j * l + a] * M[j * l + b];
+    }
+    __syncthreads();
+  }
+  for (int e = tid; e < l * l; e += nt) if ((e % l) < (e / l)) M[e] = 0.0;
+  __syncthreads();
+  return true;
+}
+
+// X = R^{-1} for upper-triangular R (thread j solves column j)
+__device__ void upper_inverse(const double* R, double* X, int l) {
+  for (int j = threadIdx.x; j < l; j += blockDim.x) {
+    for (int i = l - 1; i >= 0; --i) {
+      if (i > j) { X[i * l + j] = 0.0; continue; }
+      double s = (i == j) ? 1.0 : 0.0;
+      for (int k = i + 1; k <= j; ++k) s -= R[i * l + k] * X[k * l + j];
+      X[i * l + j] = s / R[i * l + i];
+    }
+  }
+  __syncthreads();
+}
+
+// Inverse square root of an SPD (possibly rank-deficient) matrix through Jacobi: X = V D^-1/2
+// (columns with D_i <= 1e-13 D_max are scaled as if D_i were that floor).  M is destroyed.
+__device__ void inv_sqrt_by_eig(double* M, double* V, double* X, int l, double* cs, int* pq, double* red) {
+  jacobi_eig(M, V, l, cs, pq, red);
+  double dmax = 0.0;
+  for (int i = 0; i < l; ++i) dmax = fmax(dmax, M[i * l + i]);
+  const double floor_ = fmax(dmax * 1e-13, 1e-300);
+  for (int e = threadIdx.x; e < l * l; e += blockDim.x) {
+    const int j = e % l;
+    X[e] = V[e] / sqrt(fmax(M[j * l + j], floor_));
+  }
+  __syncthreads();
+}
+
+// mode 0 (RR):    in H = Q^T Y, S = Y^T Y  -> out W (sorted Ritz vectors), lam, C = W R^-1 with R = chol(W^T S W)
+// mode 1 (CHOL):  in G                      -> out C = chol(G)^-1
+// mode 2 (FINAL): in G = sum_t Z_t^T Z_t    -> out W, lam (= sigma^2), Cemb = W diag(lam^-1/4), Cleft = W diag(lam^1/4)
+__global__ void __launch_bounds__(512) smallmat_kernel(int mode, int l, const double* __restrict__ gH, const double* __restrict__ gS,
+                                                       double* __restrict__ gW, double* __restrict__ gLam,
+                                                       double* __restrict__ gC, double* __restrict__ gC2, int* __restrict__ gFlag) {
+  extern __shared__ double smd[];
+  double* A = smd;                 // l*l
+  double* V = A + l * l;
+  double* B = V + l * l;
+  double* Cm = B + l * l;
+  double* lam = Cm + l * l;        // l
+  double* cs = lam + l;            // l
+  double* red = cs + l;            // 64
+  int* pq = (int*)(red + 64);      // l
+  __shared__ int flag;
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const int ll = l * l;
+  if (mode == 0 || mode == 2) {
+    for (int e = tid; e < ll; e += nt) { const int i = e / l, j = e % l; A[e] = 0.5 * (gH[i * l + j] + gH[j * l + i]); }
+    __syncthreads();
+    jacobi_eig(A, V, l, cs, pq, red);
+    sort_eig_desc(A, V, l, lam, B);                       // B = W
+    for (int e = tid; e < ll; e += nt) gW[e] = B[e];
+    for (int i = tid; i < l; i += nt) gLam[i] = lam[i];
+    __syncthreads();
+    if (mode == 2) {
+      for (int e = tid; e < ll; e += nt) {
+        const int j = e % l;
+        const double sig = sqrt(fmax(lam[j], 0.0));        // singular value
+        const double rt = sqrt(sig);
+        gC[e] = rt > 0.0 ? B[e] / rt : 0.0;                // Z W sigma^-1 * sigma^1/2
+        gC2[e] = B[e] * rt;                                // Q W sigma^1/2
+      }
+      return;
+    }
+    // M = W^T S W
+    for (int e = tid; e < ll; e += nt) { const int i = e / l, j = e % l; A[e] = 0.5 * (gS[i * l + j] + gS[j * l + i]); }
+    __syncthreads();
+    matmul_ll(A, B, V, l, false);                          // V = S W
+    matmul_ll(B, V, A, l, true);                           // A = W^T S W
+    for (int e = tid; e < ll; e += nt) Cm[e] = A[e];       // keep a copy for the fallback
+    __syncthreads();
+    if (cholesky_upper(A, l, &flag)) {
+      upper_inverse(A, V, l);                              // V = R^-1
+    } else {
+      for (int e = tid; e < ll; e += nt) A[e] = Cm[e];
+      __syncthreads();
+      inv_sqrt_by_eig(A, Cm, V, l, cs, pq, red);           // V = M^-1/2 factor
+    }
+    matmul_ll(B, V, A, l, false);                          // C = W * V
+    for (int e = tid; e < ll; e += nt) gC[e] = A[e];
+    if (tid == 0 && gFlag) *gFlag = flag;
+  } else {
+    for (int e = tid; e < ll; e += nt) { const int i = e / l, j = e % l; A[e] = 0.5 * (gH[i * l + j] + gH[j * l + i]); }
+    for (int e = tid; e < ll; e += nt) Cm[e] = 0.0;
+    __syncthreads();
+    for (int e = tid; e < ll; e += nt) Cm[e] = A[e];
+    __syncthreads();
+    if (cholesky_upper(A, l, &flag)) {
+      upper_inverse(A, V, l);
+    } else {
+      for (int e = tid; e < ll; e += nt) A[e] = Cm[e];
+      __syncthreads();
+      inv_sqrt_by_eig(A, B, V, l, cs, pq, red);
+    }
+    for (int e = tid; e < ll; e += nt) gC[e] = V[e];
+    if (tid == 0 && gFlag) *gFlag = flag;
+  }
+}
+
+// ---- Out[n][lo] = X[n][l] * C[l][lo]  (+ optional residual column norms) --------------------
+// 128 threads, 32 rows per tile; thread (r = tid/4, g = tid%4) computes columns g, g+4, ...
+// With resid != nullptr also accumulates ||Y W - Q W Lam||^2 per column (partials per CTA).
+__global__ void __launch_bounds__(128) apply_small_kernel(const float* __restrict__ X, int64_t n, int l, const double* __restrict__ C,
+                                                          int ldc, int lo, float* __restrict__ Out, int64_t ld_out,
+                                                          const float* __restrict__ Qm, const double* __restrict__ W,
+                                                          const double* __restrict__ lam, double* __restrict__ resid_partials,
+                                                          int tiles_per_cta) {
+  extern __shared__ double sd[];
+  double* sC = sd;                         // l * lo
+  double* sW = sC + l * lo;                // l * l (only with resid)
+  float* sx = (float*)(sW + (resid_partials ? l * l : 0));   // 32 * l
+  float* sq = sx + 32 * l;                 // 32 * l (only with resid)
+  for (int e = threadIdx.x; e < l * lo; e += 128) sC[e] = C[(e / lo) * ldc + (e % lo)];
+  if (resid_partials) for (int e = threadIdx.x; e < l * l; e += 128) sW[e] = W[e];
+  const int r = threadIdx.x >> 2, g = threadIdx.x & 3;
+  double racc[20];
+#pragma unroll
+  for (int q = 0; q < 20; ++q) racc[q] = 0.0;
+  for (int t = 0; t < tiles_per_cta; ++t) {
+    const int64_t rb = ((int64_t)blockIdx.x * tiles_per_cta + t) * 32;
+    if (rb >= n) break;
+    __syncthreads();
+    for (int e = threadIdx.x; e < 32 * l; e += 128) {
+      const int rr = e / l;
+      const bool ok = rb + rr < n;
+      sx[e] = ok ? X[(rb + rr) * l + (e - rr * l)] : 0.f;
+      if (resid_partials) sq[e] = ok ? Qm[(rb + rr) * l + (e - rr * l)] : 0.f;
+    }
+    __syncthreads();
+    const bool ok = rb + r < n;
+    for (int j = g, q = 0; j < lo; j += 4, ++q) {
+      double s = 0.0;
+      for (int k = 0; k < l; ++k) s += (double)sx[r * l + k] * sC[k * lo + j];
+      if (ok) Out[(rb + r) * ld_out + j] = (float)s;
+    }
+    if (resid_partials) {
+      for (int j = g, q = 0; j < l; j += 4, ++q) {
+        double yw = 0.0, qw = 0.0;
+        for (int k = 0; k < l; ++k) { yw += (double)sx[r * l + k] * sW[k * l + j]; qw += (double)sq[r * l + k] * sW[k * l + j]; }
+        const double d = yw - qw * lam[j];
+        racc[q] += d * d;
+      }
+    }
+  }
+  if (resid_partials) {
+    // reduce over the 32 rows of the CTA: lanes with the same g are tid = 4*r + g
+    __syncthreads();
+    double* red = sd;                      // reuse sC region: 128 * 20 doubles <= l*lo? not guaranteed -> use sW (l*l >= 256)
+    red = sW;
+    for (int q = 0; q < 20; ++q) {
+      const int j = g + 4 * q;
+      if (j >= l) break;
+      double v = racc[q];
+      // rows r and r^1.. : reduce across lanes differing in bits 2..4 of lane id, then across 4 warps via smem
+      v += __shfl_xor_sync(0xffffffffu, v, 4);
+      v += __shfl_xor_sync(0xffffffffu, v, 8);
+      v += __shfl_xor_sync(0xffffffffu, v, 16);
+      if ((threadIdx.x & 31) < 4) red[(threadIdx.x >> 5) * l + j] = v;
+    }
+    __syncthreads();
+    for (int j = threadIdx.x; j < l; j += 128)
+      resid_partials[(size_t)blockIdx.x * l + j] = red[j] + red[l + j] + red[2 * l + j] + red[3 * l + j];
+  }
+}
+
+// ---- split-transpose: X fp32 [n][l] -> Xs bf16 [3][l][n_pad] (K-major operand of the MMA) ----
+__global__ void __launch_bounds__(256) split_transpose_kernel(const float* __restrict__ X, int64_t n, int l, int64_t n_pad,
+                                                              __nv_bfloat16* __restrict__ Xs) {
+  __shared__ float t[32][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int64_t rb = (int64_t)blockIdx.x * 32;
+  const int cb = blockIdx.y * 32;
+  for (int r = ty; r < 32; r += 8) {
+    const int64_t i = rb + r; const int j = cb + tx;
+    t[r][tx] = (i < n && j < l) ? X[i * l + j] : 0.f;
+  }
+  __syncthreads();
+  for (int r = ty; r < 32; r += 8) {
+    const int j = cb + r; const int64_t i = rb + tx;
+    if (j < l && i < n_pad) {
+      __nv_bfloat16 hi, mid, lo;
+      split3(t[tx][r], hi, mid, lo);
+      Xs[((size_t)0 * l + j) * n_pad + i] = hi;
+      Xs[((size_t)1 * l + j) * n_pad + i] = mid;
+      Xs[((size_t)2 * l + j) * n_pad + i] = lo;
+    }
+  }
+}
+
+// Gaussian start block, entries keyed by (seed, row, col) -- identical on every rank
+__global__ void random_block_kernel(float* __restrict__ X, int64_t n, int l, uint64_t seed) {
+  const int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (e >= n * l) return;
+  const uint64_t h = hash4(seed, 0x51ull, (uint64_t)(e / l), (uint64_t)(e % l));
+  const float u1 = ((float)(uint32_t)(h >> 40) + 1.0f) * (1.0f / 16777216.0f);
+  const float u2 = (float)(uint32_t)((h >> 8) & 0xffffffu) * (1.0f / 16777216.0f);
+  X[e] = sqrtf(-2.0f * logf(u1)) * cospif(2.0f * u2);
+}
+
+// out = a*x + b*y + c*z elementwise (Chebyshev three-term recurrence); y or z may be null
+__global__ void axpbypcz_kernel(float* __restrict__ out, const float* __restrict__ x, double a, const float* __restrict__ y,
+                                double b, const float* __restrict__ z, double c, int64_t count) {
+  const int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (e >= count) return;
+  double v = a * (double)x[e];
+  if (y) v += b * (double)y[e];
+  if (z) v += c * (double)z[e];
+  out[e] = (float)v;
+}
+
+// ---- host wrappers ------------------------------------------------------------------------
+size_t smallmat_smem(int l) { return sizeof(double) * (4 * (size_t)l * l + 2 * l + 64) + sizeof(int) * 2 * l + 64; }
+
+int launch_xty(cudaStream_t s, const float* X, const float* Y, int64_t n, int l, double* partials, int max_parts,
+               double* out, int accumulate) {
+  int parts = (int)((n + 255) / 256);
+  if (parts > max_parts) parts = max_parts;
+  if (parts < 1) parts = 1;
+  int rows_per_cta = (int)((n + parts - 1) / parts);
+  rows_per_cta = (rows_per_cta + 31) / 32 * 32;
+  parts = (int)((n + rows_per_cta - 1) / rows_per_cta);
+  xty_kernel<<<parts, 256, sizeof(float) * 64 * l, s>>>(X, Y, n, l, rows_per_cta, partials);
+  N2V2R_CHECK_LAUNCH();
+  sum_partials_kernel<<<(l * l + 255) / 256, 256, 0, s>>>(partials, parts, l * l, out, accumulate);
+  N2V2R_CHECK_LAUNCH();
+  return N2V2R_OK;
+}
+
+int launch_smallmat(cudaStream_t s, int mode, int l, const double* H, const double* S, double* W, double* lam, double* C,
+                    double* C2, int* flag) {
+  static bool done = false;
+  if (!done) {
+    N2V2R_CUDA(cudaFuncSetAttribute(smallmat_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smallmat_smem(80)));
+    done = true;
+  }
+  smallmat_kernel<<<1, 512, smallmat_smem(l), s>>>(mode, l, H, S, W, lam, C, C2, flag);
+  N2V2R_CHECK_LAUNCH();
+  return N2V2R_OK;
+}
+
+int launch_apply_small(cudaStream_t s, const float* X, int64_t n, int l, const double* C, int ldc, int lo, float* Out, int64_t ld_out,
+                       const float* Qm, const double* W, const double* lam, double* resid_partials, int* n_parts) {
+  static bool done = false;
+  const size_t max_smem = sizeof(double) * (80 * 80 * 2) + sizeof(float) * 64 * 80;
+  if (!done) {
+    N2V2R_CUDA(cudaFuncSetAttribute(apply_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)max_smem));
+    done = true;
+  }
+  const int64_t tiles = (n + 31) / 32;
+  int grid = (int)(tiles < (int64_t)sm_count() * 4 ? tiles : (int64_t)sm_count() * 4);
+  const int tiles_per_cta = (int)((tiles + grid - 1) / grid);
+  grid = (int)((tiles + tiles_per_cta - 1) / tiles_per_cta);
+  const size_t smem = sizeof(double) * ((size_t)l * lo + (resid_partials ? (size_t)l * l : 0)) +
+                      sizeof(float) * 32 * l * (resid_partials ? 2 : 1);
+  apply_small_kernel<<<grid, 128, smem, s>>>(X, n, l, C, ldc, lo, Out, ld_out, Qm, W, lam, resid_partials, tiles_per_cta);
+  N2V2R_CHECK_LAUNCH();
+  if (n_parts) *n_parts = grid;
+  return N2V2R_OK;
+}
+
+int launch_sum_partials(cudaStream_t s, const double* partials, int n_parts, int count, double* out) {
+  sum_partials_kernel<<<(count + 255) / 256, 256, 0, s>>>(partials, n_parts, count, out, 0);
+  N2V2R_CHECK_LAUNCH();
+  return N2V2R_OK;
+}
+
+int launch_split_transpose(cudaStream_t s, const float* X, int64_t n, int l, int64_t n_pad, __nv_bfloat16* Xs) {
+  dim3 grid((unsigned)((n_pad + 31) / 32), (unsigned)((l + 31) / 32));
+  split_transpose_kernel<<<grid, 256, 0, s>>>(X, n, l, n_pad, Xs);
+  N2V2R_CHECK_LAUNCH();
+  return N2V2R_OK;
+}
+
+int launch_random_block(cudaStream_t s, float* X, int64_t n, int l, uint64_t seed) {
+  const int64_t cnt = n * l;
+  random_block_kernel<<<(unsigned)((cnt + 255) / 256), 256, 0, s>>>(X, n, l, seed);
+  N2V2R_CHECK_LAUNCH();
+  return N2V2R_OK;
+}
+
+int launch_axpbypcz(cudaStream_t s, float* out, const float* x, double a, const float* y, double b, const float* z, double c,
+                    int64_t count) {
+  axpbypcz_kernel<<<(unsigned)((count + 255) / 256), 256, 0, s>>>(out, x, a, y, b, z, c, count);
+  N2V2R_CHECK_LAUNCH();
+  return N2V2R_OK;
+}
+
+}  // namespace n2v2r

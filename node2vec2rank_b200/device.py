@@ -1,0 +1,301 @@
+"""Device-side operators: thin Python over the C ABI (torch tensors own the memory).
+
+Every function here runs hand-written sm_100a kernels through libn2v2r_b200.so; nothing
+falls back to the CPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+
+import numpy as np
+import torch
+
+from . import _native as N
+
+
+def _dev():
+    return N.require_gpu()
+
+
+@dataclass
+class DeviceLayer:
+    """A preprocessed graph layer resident in HBM as bf16 planes (see include/n2v2r_b200.h)."""
+    planes: torch.Tensor            # (P, n, ld) bf16
+    n: int
+    ld: int
+    n_planes: int
+    symmetric: bool = True
+    planes_t: torch.Tensor | None = None
+    colsum: torch.Tensor | None = None     # (n,) float64, column sums of the fp32 values
+    shape: tuple = field(default=())
+    dtype = np.float32
+
+    def __post_init__(self):
+        self.shape = (self.n, self.n)
+
+    def c_struct(self):
+        return N.Layer(self.planes.data_ptr(), 0 if self.planes_t is None else self.planes_t.data_ptr(),
+                       self.n_planes, 0, self.ld)
+
+    def to_dense(self):
+        """fp32 (n, n) device tensor reconstructed from the planes (exact for P planes)."""
+        return self.planes[:, :, :self.n].to(torch.float32).sum(dim=0)
+
+    def numpy(self):
+        return self.to_dense().cpu().numpy()
+
+    def __array__(self, dtype=None, copy=None):
+        a = self.numpy()
+        return a if dtype is None else a.astype(dtype)
+
+    @property
+    def nbytes(self):
+        return self.planes.numel() * 2 * (2 if self.planes_t is not None else 1)
+
+
+def _dtype_code(t: torch.Tensor):
+    if t.dtype == torch.float32:
+        return N.F32
+    if t.dtype == torch.float64:
+        return N.F64
+    raise TypeError(f"unsupported dtype {t.dtype}; expected float32 or float64")
+
+
+def to_device(x):
+    """Host array (float32/float64, anything else is cast to float64 like pandas would) -> contiguous device tensor."""
+    dev = _dev()
+    if isinstance(x, torch.Tensor):
+        t = x
+    else:
+        a = np.asarray(getattr(x, "values", x))
+        if a.dtype not in (np.float32, np.float64):
+            a = a.astype(np.float64)
+        t = torch.from_numpy(np.ascontiguousarray(a))
+    if t.dtype not in (torch.float32, torch.float64):
+        t = t.to(torch.float64)
+    return t.to(dev, non_blocking=True).contiguous()
+
+
+def sbm_generate(n, K, B, seed, layer, weighted=False):
+    """K0: synthetic SBM layer on the device, fp32 (n, n)."""
+    dev = _dev()
+    ld = (n + 3) // 4 * 4
+    out = torch.empty((n, ld), dtype=torch.float32, device=dev)
+    Bh = np.ascontiguousarray(np.asarray(B, dtype=np.float32).reshape(K, K))
+    N.check(N.load().n2v2r_sbm_generate(N.stream_ptr(), N.ptr(out), n, ld, K,
+                                        Bh.ctypes.data_as(C.POINTER(C.c_float)), C.c_uint64(seed), layer, int(weighted)))
+    return out if ld == n else out[:, :n].contiguous()
+
+
+def select_nonzero(x: torch.Tensor, frac: float, absolute=False, threshold=None):
+    """K1a: (nnz, v_lo, v_hi, virtual_index) of the nonzeros of the (abs/thresholded) matrix."""
+    lib = N.load()
+    ws = torch.empty(lib.n2v2r_select_workspace_bytes(), dtype=torch.uint8, device=x.device)
+    nnz, lo, hi, pos = C.c_int64(), C.c_double(), C.c_double(), C.c_double()
+    rows, cols = x.shape
+    N.check(lib.n2v2r_select_nonzero(N.stream_ptr(), N.ptr(x), _dtype_code(x), rows, cols, cols, int(bool(absolute)),
+                                     int(threshold is not None), float(threshold or 0.0), float(frac),
+                                     int(x.dtype == torch.float32), N.ptr(ws), ws.numel(),
+                                     C.byref(nnz), C.byref(lo), C.byref(hi), C.byref(pos)))
+    return nnz.value, lo.value, hi.value, pos.value
+
+
+def percentile_cut(x: torch.Tensor, q, absolute=False, threshold=None):
+    """np.percentile(y[y.nonzero()], q) with NumPy's 'linear' method, the order statistics coming
+    from the device radix select (preprocessing_utils.py:134).  The interpolation follows
+    numpy/lib/_function_base_impl.py (_quantile/_lerp) in the dtype of the data."""
+    ft = np.float32 if x.dtype == torch.float32 else np.float64
+    quant = np.true_divide(q, ft(100))                 # percentile(): q / a.dtype.type(100)
+    nnz, lo, hi, pos = select_nonzero(x, float(quant), absolute, threshold)
+    if nnz == 0:
+        raise IndexError("index -1 is out of bounds for axis 0 with size 0")   # what np.percentile raises on empty input
+    virt = ft(pos)
+    prev = np.floor(virt)
+    gamma = ft(np.float64(virt) - prev)
+    a, b, t = ft(lo), ft(hi), gamma
+    diff = b - a
+    lerp = a + diff * t
+    if t >= 0.5:
+        lerp = b - diff * (1 - t)
+    return lerp
+
+
+def planes_needed(x32: torch.Tensor):
+    need = C.c_int(1)
+    rows, cols = x32.shape
+    N.check(N.load().n2v2r_planes_needed(N.stream_ptr(), N.ptr(x32), rows, cols, x32.stride(0), C.byref(need)))
+    return need.value
+
+
+def transform(x: torch.Tensor, absolute=False, threshold=None, cut=None, binarize=False,
+              want_f32=False, n_planes=0, want_colsum=False):
+    """K1b fused load pass.  Returns (out_f32 | None, planes | None, ld_p, colsum | None)."""
+    lib = N.load()
+    rows, cols = x.shape
+    out = torch.empty((rows, cols), dtype=torch.float32, device=x.device) if want_f32 else None
+    ld_p = (cols + 63) // 64 * 64
+    planes = torch.empty((n_planes, rows, ld_p), dtype=torch.bfloat16, device=x.device) if n_planes else None
+    colsum = torch.zeros(cols, dtype=torch.float64, device=x.device) if want_colsum else None
+    N.check(lib.n2v2r_transform(N.stream_ptr(), N.ptr(x), _dtype_code(x), rows, cols, x.stride(0),
+                                int(bool(absolute)), int(threshold is not None), float(threshold or 0.0),
+                                int(cut is not None), float(cut if cut is not None else 0.0), int(bool(binarize)),
+                                N.ptr(out), cols, N.ptr(planes), n_planes, ld_p, N.ptr(colsum)))
+    return out, planes, ld_p, colsum
+
+
+def project(W: torch.Tensor, on):
+    """K2: W^T W ('columns') or W W^T ('rows') on the tensor cores -> fp32 device matrix."""
+    lib = N.load()
+    which = on.casefold()                       # AttributeError on None, like the reference
+    if which not in ("columns", "rows"):
+        raise ValueError("Unknown projection type, options are columns or rows")
+    rows, cols = W.shape
+    assert rows != cols, "Graph is not bipartite"
+    on_rows = int(which == "rows")
+    m = rows if on_rows else cols
+    ws = torch.empty(lib.n2v2r_project_workspace_bytes(rows, cols, on_rows), dtype=torch.uint8, device=W.device)
+    out = torch.empty((m, m), dtype=torch.float32, device=W.device)
+    N.check(lib.n2v2r_project(N.stream_ptr(), N.ptr(W), _dtype_code(W), rows, cols, W.stride(0), on_rows,
+                              N.ptr(out), m, N.ptr(ws), ws.numel()))
+    return out
+
+
+def make_layer(x32: torch.Tensor, n_planes=None, colsum=None, check_symmetry=True):
+    """fp32 (n, n) device matrix -> DeviceLayer (planes + symmetry flag / transposed copy)."""
+    lib = N.load()
+    n = x32.shape[0]
+    assert x32.shape[0] == x32.shape[1], "layer must be square"
+    P = n_planes or planes_needed(x32)
+    _, planes, ld_p, cs = transform(x32, n_planes=P, want_colsum=colsum is None)
+    return finish_layer(planes, n, ld_p, P, cs if colsum is None else colsum, check_symmetry)
+
+
+def finish_layer(planes, n, ld_p, P, colsum, check_symmetry=True):
+    lib = N.load()
+    sym = C.c_int(1)
+    planes_t = None
+    if check_symmetry:
+        N.check(lib.n2v2r_is_symmetric(N.stream_ptr(), N.ptr(planes), P, n, ld_p, C.byref(sym)))
+        if not sym.value:
+            planes_t = torch.empty_like(planes)
+            N.check(lib.n2v2r_transpose_planes(N.stream_ptr(), N.ptr(planes), P, n, ld_p, N.ptr(planes_t)))
+    return DeviceLayer(planes=planes, n=n, ld=ld_p, n_planes=P, symmetric=bool(sym.value), planes_t=planes_t, colsum=colsum)
+
+
+def preprocess_to_layer(x: torch.Tensor, threshold=None, top_percent_keep=100, binarize=False, absolute=False,
+                        project_unipartite_on="columns", storage_planes=None, want_f32=False):
+    """network_transform (preprocessing_utils.py:116-141) on the device.
+
+    Returns (DeviceLayer, out_f32 | None).  Order of operations as the reference: abs ->
+    threshold -> projection when non-square -> percentile cut over the nonzeros -> binarize
+    -> fp32.  The select and apply kernels share one element transform, so the cut is taken
+    on exactly the values it is applied to."""
+    rows, cols = x.shape
+    if rows != cols:
+        if absolute or threshold is not None:
+            x, _, _, _ = transform(x, absolute=absolute, threshold=threshold, want_f32=True)
+        x = project(x, project_unipartite_on)
+        absolute, threshold = False, None
+    cut = percentile_cut(x, 100 - top_percent_keep, absolute, threshold)          # runs even for keep == 100 (:134)
+    n = x.shape[0]
+    if binarize:
+        P = 1
+    elif storage_planes:
+        P = int(storage_planes)
+    else:
+        P = 0
+    if P == 0:
+        # exact storage: materialise fp32 once, count the planes it needs, then split
+        out, _, _, cs = transform(x, absolute, threshold, float(cut), binarize, want_f32=True, want_colsum=True)
+        layer = make_layer(out, colsum=cs)
+        return layer, (out if want_f32 else None)
+    out, planes, ld_p, cs = transform(x, absolute, threshold, float(cut), binarize, want_f32=want_f32, n_planes=P,
+                                      want_colsum=True)
+    return finish_layer(planes, n, ld_p, P, cs), out
+
+
+def uase(layers, k, l=64, tol=1e-5, max_iters=300, min_iters=2, seed=42, check_dims=None, algo=N.ALGO_TCGEN05,
+         k_chunk=0, allreduce=None, T_global=None, layer_offset=0, want_left=False):
+    """K3-K8: returns (embeddings (T_local, n, k) fp32 device, sigma (k,) float64, left | None, stats dict)."""
+    lib = N.load()
+    dev = _dev()
+    T = len(layers)
+    n = layers[0].n
+    dims = np.asarray(sorted(set(int(d) for d in (check_dims or [k]) if 1 <= int(d) <= k)), dtype=np.int32)
+    p = N.UaseParams(n=n, T_local=T, T_global=T_global or T, layer_offset=layer_offset, k=k, l=l,
+                     max_iters=max_iters, min_iters=min_iters, cheb_degree=1, algo=algo, k_chunk=k_chunk,
+                     n_check=len(dims), tol=tol, seed=seed,
+                     h_check_dims=dims.ctypes.data_as(C.POINTER(C.c_int32)))
+    ws_bytes = lib.n2v2r_uase_workspace_bytes(C.byref(p))
+    if ws_bytes == 0:
+        raise N.NativeError(N.EINVAL, lib.n2v2r_last_error().decode())
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+    emb = torch.empty((T, n, k), dtype=torch.float32, device=dev)
+    left = torch.empty((n, k), dtype=torch.float32, device=dev) if want_left else None
+    sigma = np.zeros(k, dtype=np.float64)
+    stats = N.UaseStats()
+    arr = (N.Layer * T)(*[L.c_struct() for L in layers])
+    cb = N.ALLREDUCE_FN(allreduce) if allreduce is not None else C.cast(None, N.ALLREDUCE_FN)
+    rc = lib.n2v2r_uase(N.stream_ptr(), C.byref(p), arr, N.ptr(ws), ws_bytes, cb, None, N.ptr(emb), N.ptr(left),
+                        sigma.ctypes.data_as(C.POINTER(C.c_double)), C.byref(stats))
+    N.check(rc, allow=(N.ENOTCONV,))
+    info = dict(iterations=stats.iterations, layer_passes=stats.layer_passes, converged=bool(stats.converged),
+                kernel_launches=stats.kernel_launches, stream_ms=stats.stream_ms, total_ms=stats.total_ms,
+                stream_bytes=stats.stream_bytes, angle_bound=stats.max_angle_bound,
+                resid=np.asarray(stats.resid[:l]), ritz=np.asarray(stats.ritz[:l]), status=rc, l=l)
+    return emb, sigma, left, info
+
+
+def layer_apply(layer: DeviceLayer, x: torch.Tensor, transpose=False, algo=N.ALGO_TCGEN05, k_chunk=0, ws=None):
+    """One streaming skinny product (K3/K4): A x or A^T x, x (n, l) fp32."""
+    lib = N.load()
+    n, l = x.shape
+    out = torch.empty_like(x)
+    if ws is None:
+        ws = torch.empty(lib.n2v2r_apply_workspace_bytes(n, l, k_chunk), dtype=torch.uint8, device=x.device)
+    st = layer.c_struct()
+    N.check(lib.n2v2r_layer_apply(N.stream_ptr(), C.byref(st), n, l, int(transpose), N.ptr(x), N.ptr(out), algo, k_chunk,
+                                  N.ptr(ws), ws.numel()))
+    return out
+
+
+def column_specs(embed_dimensions, distance_metrics):
+    """Column order of model.py:73-90: dims outer, metrics inner, cosine skipped at d == 1."""
+    names, dims, mets = [], [], []
+    for d in embed_dimensions:
+        for m in distance_metrics:
+            if m == "cosine" and d == 1:
+                continue
+            if m not in N.METRICS:
+                raise NotImplementedError("Unsupported metric")        # model_utils.py:65
+            names.append(f"dim-{d}_distance-{m}")
+            dims.append(int(d))
+            mets.append(N.METRICS[m])
+    return names, np.asarray(dims, dtype=np.int32), np.asarray(mets, dtype=np.int32)
+
+
+def distances(emb: torch.Tensor, col_dims, col_metrics, strategy):
+    """K9: scores (n_comparisons, n_cols, n) float64 on the device."""
+    lib = N.load()
+    T, n, k = emb.shape
+    n_comp = T if strategy == N.ONE_VS_REST else T - 1
+    n_cols = len(col_dims)
+    scores = torch.empty((max(n_comp, 0), n_cols, n), dtype=torch.float64, device=emb.device)
+    if n_comp > 0 and n_cols > 0:
+        N.check(lib.n2v2r_distances(N.stream_ptr(), N.ptr(emb.contiguous()), T, n, k,
+                                    col_dims.ctypes.data_as(C.POINTER(C.c_int32)),
+                                    col_metrics.ctypes.data_as(C.POINTER(C.c_int32)), n_cols, strategy, N.ptr(scores)))
+    return scores
+
+
+def rank_borda(scores: torch.Tensor, want_positions=False):
+    """K10+K11: scores (n_cols, n) float64 -> (borda (n,) int64, positions (n_cols, n) int32 | None)."""
+    lib = N.load()
+    n_cols, n = scores.shape
+    ws = torch.empty(lib.n2v2r_rank_workspace_bytes(n, n_cols), dtype=torch.uint8, device=scores.device)
+    borda = torch.empty(n, dtype=torch.int64, device=scores.device)
+    pos = torch.empty((n_cols, n), dtype=torch.int32, device=scores.device) if want_positions else None
+    N.check(lib.n2v2r_rank_borda(N.stream_ptr(), N.ptr(scores.contiguous()), n, n_cols, N.ptr(pos), N.ptr(borda),
+                                 N.ptr(ws), ws.numel()))
+    return borda, pos
