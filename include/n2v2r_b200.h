@@ -183,12 +183,12 @@ int n2v2r_layer_apply(void* stream, const n2v2r_layer_t* h_layer, int64_t n, int
 /* ------------------------------------------------------------------------------------
  * K9  per-node distances for every swept d.  Replaces N2V2R.__rank (model.py:57-96) +
  * compute_pairwise_distances (model_utils.py:39-67).
- * d_embed: (T x n x k) fp32.  Column c uses the leading h_col_dim[c] components and metric
+ * d_embed: (T x n x k), dtype F32 or F64.  Column c uses the leading h_col_dim[c] components and metric
  * h_col_metric[c].  Comparisons follow `strategy`: sequential / one_vs_before give
  * T-1 comparisons (layers 1..T-1), one_vs_rest gives T.  float64 arithmetic.
  * d_scores: (n_comparisons x n_cols x n) doubles, each column contiguous.
  * ---------------------------------------------------------------------------------- */
-int n2v2r_distances(void* stream, const float* d_embed, int T, int64_t n, int k,
+int n2v2r_distances(void* stream, const void* d_embed, int dtype, int T, int64_t n, int k,
                     const int32_t* h_col_dim, const int32_t* h_col_metric, int n_cols,
                     int strategy, double* d_scores);
 

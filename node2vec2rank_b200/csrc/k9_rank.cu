@@ -9,8 +9,8 @@ namespace n2v2r {
 constexpr int kMaxK = 96;
 
 // One thread per node.  `one` = reference layer (or mean of layers), `two` = layer i.
-template <int KMAX>
-__global__ void __launch_bounds__(128) distances_kernel(const float* __restrict__ emb, int T, int64_t n, int k,
+template <int KMAX, class E>
+__global__ void __launch_bounds__(128) distances_kernel(const E* __restrict__ emb, int T, int64_t n, int k,
                                                         const int* __restrict__ col_dim, const int* __restrict__ col_metric,
                                                         int n_cols, int strategy, double* __restrict__ scores) {
   const int64_t node = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
@@ -151,12 +151,13 @@ __global__ void __launch_bounds__(1024) rank_sort_kernel(const double* __restric
 
 using namespace n2v2r;
 
-extern "C" int n2v2r_distances(void* stream, const float* d_embed, int T, int64_t n, int k,
+extern "C" int n2v2r_distances(void* stream, const void* d_embed, int dtype, int T, int64_t n, int k,
                                const int32_t* h_col_dim, const int32_t* h_col_metric, int n_cols,
                                int strategy, double* d_scores) {
   N2V2R_REQUIRE(d_embed && d_scores && h_col_dim && h_col_metric, "distances: null pointer");
   N2V2R_REQUIRE(T >= 1 && n > 0 && k >= 1 && k <= kMaxK && n_cols >= 1, "distances: bad shape (k <= %d)", kMaxK);
   N2V2R_REQUIRE(strategy >= 0 && strategy <= 2, "distances: unknown strategy %d", strategy);
+  N2V2R_REQUIRE(dtype == N2V2R_F32 || dtype == N2V2R_F64, "distances: unknown dtype %d", dtype);
   for (int c = 0; c < n_cols; ++c) {
     N2V2R_REQUIRE(h_col_dim[c] >= 1 && h_col_dim[c] <= k, "distances: column %d dim %d outside [1,%d]", c, h_col_dim[c], k);
     N2V2R_REQUIRE(h_col_metric[c] >= 0 && h_col_metric[c] <= 2, "distances: unsupported metric code %d", h_col_metric[c]);
@@ -169,10 +170,16 @@ extern "C" int n2v2r_distances(void* stream, const float* d_embed, int T, int64_
   N2V2R_CUDA(cudaMemcpyAsync(d_meta, h_col_dim, sizeof(int) * n_cols, cudaMemcpyHostToDevice, s));
   N2V2R_CUDA(cudaMemcpyAsync(d_meta + n_cols, h_col_metric, sizeof(int) * n_cols, cudaMemcpyHostToDevice, s));
   dim3 grid((unsigned)((n + 127) / 128), (unsigned)n_comp);
-  if (k <= 32)
-    distances_kernel<32><<<grid, 128, 0, s>>>(d_embed, T, n, k, d_meta, d_meta + n_cols, n_cols, strategy, d_scores);
-  else
-    distances_kernel<kMaxK><<<grid, 128, 0, s>>>(d_embed, T, n, k, d_meta, d_meta + n_cols, n_cols, strategy, d_scores);
+  const int* cd = d_meta; const int* cm = d_meta + n_cols;
+  if (dtype == N2V2R_F32) {
+    const float* e = (const float*)d_embed;
+    if (k <= 32) distances_kernel<32, float><<<grid, 128, 0, s>>>(e, T, n, k, cd, cm, n_cols, strategy, d_scores);
+    else distances_kernel<kMaxK, float><<<grid, 128, 0, s>>>(e, T, n, k, cd, cm, n_cols, strategy, d_scores);
+  } else {
+    const double* e = (const double*)d_embed;
+    if (k <= 32) distances_kernel<32, double><<<grid, 128, 0, s>>>(e, T, n, k, cd, cm, n_cols, strategy, d_scores);
+    else distances_kernel<kMaxK, double><<<grid, 128, 0, s>>>(e, T, n, k, cd, cm, n_cols, strategy, d_scores);
+  }
   N2V2R_CHECK_LAUNCH();
   N2V2R_CUDA(cudaFreeAsync(d_meta, s));
   return N2V2R_OK;

@@ -283,7 +283,8 @@ def distances(emb: torch.Tensor, col_dims, col_metrics, strategy):
     n_cols = len(col_dims)
     scores = torch.empty((max(n_comp, 0), n_cols, n), dtype=torch.float64, device=emb.device)
     if n_comp > 0 and n_cols > 0:
-        N.check(lib.n2v2r_distances(N.stream_ptr(), N.ptr(emb.contiguous()), T, n, k,
+        emb = emb.contiguous()
+        N.check(lib.n2v2r_distances(N.stream_ptr(), N.ptr(emb), _dtype_code(emb), T, n, k,
                                     col_dims.ctypes.data_as(C.POINTER(C.c_int32)),
                                     col_metrics.ctypes.data_as(C.POINTER(C.c_int32)), n_cols, strategy, N.ptr(scores)))
     return scores
@@ -299,3 +300,17 @@ def rank_borda(scores: torch.Tensor, want_positions=False):
     N.check(lib.n2v2r_rank_borda(N.stream_ptr(), N.ptr(scores.contiguous()), n, n_cols, N.ptr(pos), N.ptr(borda),
                                  N.ptr(ws), ws.numel()))
     return borda, pos
+
+
+def default_block_width(k, n):
+    """Solver block width l: k plus a buffer of guard vectors, a multiple of 16 in [16, 80], < n when possible."""
+    l = ((k + 24 + 15) // 16) * 16
+    l = max(16, min(80, l))
+    while l > 16 and l >= n:
+        l -= 16
+    return l
+
+
+def column_sums(layer: DeviceLayer):
+    """Column sums (float64, device) of a DeviceLayer: sum over planes of the bf16 values (model.py:293-294)."""
+    return layer.planes[:, :, :layer.n].to(torch.float64).sum(dim=(0, 1))

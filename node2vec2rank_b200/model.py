@@ -1,0 +1,234 @@
+"""Mirror of node2vec2rank/model.py (class N2V2R, :17-311) with fit / rank / Borda on the B200.
+
+Public surface kept verbatim: constructor argument order (graphs, nodes, config), attributes
+(node_embeddings, pairwise_ranks, pairwise_aggregate_ranks, pairwise_signed_ranks,
+pairwise_signed_aggregate_ranks, prior_singed_ranks, save_dir), methods, prints, output files
+and exceptions.  `graphs` may be float32 ndarrays (what the reference's DataLoader returns) or
+device.DeviceLayer objects (DataLoader with "device_resident": true).
+
+Additive, optional config keys (defaults keep reference behaviour):
+  block_width (int, default: max dim + >=24 guard vectors rounded up to 16): solver block l
+  solver_tol (float, default 1e-5), solver_max_iters (int, default 400)
+  storage_planes (int | None): bf16 planes per weighted layer (None = exact)
+"""
+from __future__ import annotations
+
+import json
+import os
+import random
+import time
+from datetime import datetime
+
+import numpy as np
+import pandas as pd
+import torch
+
+from . import _native as N
+from . import device as D
+from .model_utils import signed_transform_single
+
+
+class N2V2R:
+    def __init__(self, graphs: list, nodes: list, config: dict):
+        self.config = config
+        self.node_names = nodes
+        self.graphs = graphs
+        self.num_graphs = len(graphs)
+        self.embed_dimensions = self.config['embed_dimensions']
+        self.max_embed_dim = max(self.embed_dimensions)
+        self.distance_metrics = self.config['distance_metrics']
+        self.save_dir = None
+        self.comp_strategy = self.config['comp_strategy']
+
+        self.node_embeddings = None
+        self.pairwise_ranks = None
+        self.pairwise_signed_ranks = None
+        self.pairwise_aggregate_ranks = None
+        self.pairwise_signed_aggregate_ranks = None
+        self.prior_singed_ranks = None
+        self.singular_values = None
+        self.solver_info = None
+        self._layers = None            # device-resident layers (built lazily, reused by DeDi)
+        self._emb_dev = None
+        self._scores_dev = None
+
+        if self.config["seed"]:        # falsy seed (None or 0) => unseeded, model.py:36
+            random.seed(self.config["seed"])
+            np.random.seed(self.config["seed"])
+
+        now = datetime.now().strftime(r"%m_%d_%Y_%H_%M_%S")
+        if self.config["save_dir"]:
+            self.save_dir = os.path.join(self.config["save_dir"], now)
+            print(self.save_dir)
+            os.makedirs(self.save_dir)
+            with open(os.path.join(self.save_dir, "config.json"), 'w', encoding="utf-8") as f:
+                json.dump(self.config, f)
+
+    # ---- device residency -----------------------------------------------------------------
+    def _device_layers(self):
+        if self._layers is None:
+            layers = []
+            for g in self.graphs:
+                if isinstance(g, D.DeviceLayer):
+                    layers.append(g)
+                else:
+                    x = D.to_device(np.asarray(g))
+                    if x.dtype != torch.float32:        # the reference hands fp32 to the SVD (preprocessing_utils.py:141)
+                        x = x.to(torch.float32)
+                    layers.append(D.make_layer(x, n_planes=self.config.get("storage_planes")))
+            self._layers = layers
+        return self._layers
+
+    def _solver_seed(self):
+        seed = self.config.get("seed")
+        if seed:
+            return int(seed)
+        return int(np.random.randint(0, 2**31 - 1))     # unseeded run: draw from the global RNG like svds' v0
+
+    # ---- fit: replaces model.py:51-55 (csc_matrix + spectral_embedding.UASE) ----------------
+    def __fit(self, graphs):
+        layers = self._device_layers()
+        n = layers[0].n
+        k = self.max_embed_dim
+        if k >= n:                                      # scipy svds: "k must satisfy 0 < k < min(A.shape)"
+            raise ValueError(f"`k` must be an integer satisfying `0 < k < min(A.shape)` (k={k}, n={n}).")
+        l = int(self.config.get("block_width") or D.default_block_width(k, n))
+        emb, sigma, _, info = D.uase(layers, k, l=l, tol=float(self.config.get("solver_tol", 1e-5)),
+                                     max_iters=int(self.config.get("solver_max_iters", 400)),
+                                     seed=self._solver_seed(), check_dims=self.embed_dimensions)
+        self._emb_dev = emb
+        self.singular_values = sigma
+        self.solver_info = info
+        # float64 container holding fp32-precision values, like se.UASE's YA
+        self.node_embeddings = emb.cpu().numpy().astype(np.float64)
+
+    # ---- rank: replaces model.py:57-96 + model_utils.py:39-67 --------------------------------
+    def __rank(self, pairwise_ranks_dict, comp_strategy):
+        if comp_strategy not in N.STRATEGIES:
+            raise UnboundLocalError("cannot access local variable 'embed_one' where it is not associated with a value")
+        names, dims, mets = D.column_specs(self.embed_dimensions, self.distance_metrics)
+        strategy = N.STRATEGIES[comp_strategy]
+        scores = D.distances(self._emb_dev, dims, mets, strategy)        # (C, cols, n) float64
+        self._scores_dev = {}
+        host = scores.cpu().numpy()
+        for c in range(scores.shape[0]):
+            key = str(c + 1)                                             # '1'..'T-1' or '1'..'T'
+            table = pd.DataFrame(host[c].T, index=self.node_names, columns=names)
+            pairwise_ranks_dict.setdefault(key, []).append(table)
+            self._scores_dev[key] = scores[c]
+
+    def fit_transform_rank(self):
+        """Differential scores of every node for every comparison: dict key -> DataFrame
+        (index = node names, one column per (dim, metric)); writes <key>.tsv."""
+        if self.config["verbose"] >= 0:
+            print(f"\nRunning n2v2r with dimensions {self.embed_dimensions} and distance metrics {self.distance_metrics} ...")
+        tic_n2v2r = time.time()
+        pairwise_ranks_dict = {}
+        tic_uase = time.time()
+        self.__fit(graphs=self.graphs)
+        toc_uase = time.time()
+        if self.config["verbose"] == 1:
+            print(f"""\tMulti-layer embedding in {round(toc_uase - tic_uase, 2)} seconds""")
+        self.__rank(pairwise_ranks_dict=pairwise_ranks_dict, comp_strategy=self.comp_strategy)
+        self.pairwise_ranks = {key: pd.concat(pairwise_ranks_dict[key], axis=1) for key in pairwise_ranks_dict}
+        num_rankings = sum([len(self.pairwise_ranks[key].columns) for key in self.pairwise_ranks])
+        toc_n2v2r = time.time()
+        if self.config["verbose"] >= 0:
+            print(f"""n2v2r computed {num_rankings} rankings for {len(self.pairwise_ranks)} comparison(s) in {round(toc_n2v2r - tic_n2v2r, 2)} seconds""")
+        if self.config["save_dir"]:
+            for key, rank in self.pairwise_ranks.items():
+                rank.to_csv(os.path.join(self.save_dir, key + ".tsv"), sep='\t', index=True)
+        return self.pairwise_ranks
+
+    # ---- Borda: replaces model.py:149-201 + model_utils.py:22-36 -----------------------------
+    def aggregate_transform(self, method='Borda'):
+        """Borda aggregation of every comparison's columns: dict key -> DataFrame('borda_ranks', int64)
+        in node order; writes <key>_agg.tsv.  Ties are broken by node position (stable), NaN last."""
+        if self.pairwise_ranks:
+            out = {}
+            start_time = time.time()
+            if self.config["verbose"] >= 0:
+                print("\nRank aggregation with Borda ...")
+            dev = N.require_gpu()
+            for comparison_key in self.pairwise_ranks:
+                if method.casefold() != 'borda':
+                    raise NotImplementedError('Aggregation method not found. Available methods: Borda')
+                table = self.pairwise_ranks[comparison_key]
+                cached = (self._scores_dev or {}).get(comparison_key)
+                if cached is not None and cached.shape == (table.shape[1], table.shape[0]):
+                    scores = cached
+                else:                                    # user-supplied / modified table
+                    scores = torch.from_numpy(np.ascontiguousarray(table.to_numpy(dtype=np.float64).T)).to(dev)
+                borda, _ = D.rank_borda(scores)
+                out[comparison_key] = pd.DataFrame(borda.cpu().numpy(), index=self.node_names, columns=['borda_ranks'])
+            self.pairwise_aggregate_ranks = out
+            exec_time_agg = round(time.time() - start_time, 2)
+            if self.config["verbose"] == 1:
+                print(f"\tFinished aggregation in {exec_time_agg} seconds")
+            if self.config["save_dir"]:
+                for k, rank in self.pairwise_aggregate_ranks.items():
+                    rank.to_csv(os.path.join(self.save_dir, k + "_agg.tsv"), sep='\t', index=True)
+        else:
+            raise ValueError("No n2v2r embeddings found")
+        return self.pairwise_aggregate_ranks
+
+    # ---- signed ranks: model.py:203-280 (host-side select over the score tables) -------------
+    def signed_ranks_transform(self, prior_signed_ranks: pd.Series = None):
+        if prior_signed_ranks is None:
+            if self.prior_singed_ranks:
+                prior_signed_ranks = self.prior_singed_ranks
+            else:
+                raise ValueError("""Prior signed ranks needed, run degree_difference_ranking beforehand
+                                 or provide them in arguments.""")
+        if self.pairwise_ranks:
+            print("\nSigned ranks transformation ...")
+            start_time = time.time()
+            signed, signed_agg = {}, {}
+            for index, comparison_key in enumerate(self.pairwise_ranks):
+                table = self.pairwise_ranks[comparison_key]
+                prior = prior_signed_ranks[index]
+                cols = {}
+                last = None
+                for name in table.columns:
+                    last = signed_transform_single(table[name], prior)
+                    cols[name] = last.values
+                frame = pd.DataFrame(cols)
+                frame.index = last.index
+                signed[comparison_key] = frame
+                if self.pairwise_aggregate_ranks:
+                    s = signed_transform_single(self.pairwise_aggregate_ranks[comparison_key].iloc[:, 0], prior)
+                    signed_agg[comparison_key] = pd.DataFrame(s.values, index=s.index, columns=["signed_agg_ranks"])
+        self.pairwise_signed_ranks = signed
+        if self.pairwise_aggregate_ranks:
+            self.pairwise_signed_aggregate_ranks = signed_agg
+        exec_time_signed = round(time.time() - start_time, 2)
+        if self.config["verbose"] == 1:
+            print(f"\tFinished signed transformation in {exec_time_signed} seconds")
+        if self.config["save_dir"]:
+            for k in self.pairwise_signed_ranks:
+                self.pairwise_signed_ranks[k].to_csv(os.path.join(self.save_dir, k + "_signed.tsv"), sep='\t', index=True)
+            if self.pairwise_aggregate_ranks:
+                for k in self.pairwise_signed_aggregate_ranks:
+                    self.pairwise_signed_aggregate_ranks[k].to_csv(os.path.join(self.save_dir, str(k) + "_agg_signed.tsv"),
+                                                                   sep='\t', index=True)
+        return self.pairwise_signed_ranks
+
+    # ---- DeDi: model.py:282-311; the column sums are a by-product of the load pass (K1b) -----
+    def degree_difference_ranking(self):
+        layers = self._device_layers()
+        sums = []
+        for L in layers:
+            if L.colsum is None:
+                L.colsum = D.column_sums(L)
+            sums.append(L.colsum.cpu().numpy().astype(np.float32))      # np.sum of an fp32 matrix is fp32
+        pairwise = {}
+        for i in range(1, len(layers)):
+            DeDi = sums[i - 1] - sums[i]
+            ranking = pd.DataFrame.from_dict({"DeDi": DeDi, "absDeDi": np.abs(DeDi)})
+            ranking.index = self.node_names
+            pairwise[str(i)] = ranking
+        self.prior_singed_ranks = [v.iloc[:, 0] for k, v in pairwise.items()]
+        if self.config["save_dir"]:
+            for k, rank in pairwise.items():
+                rank.to_csv(os.path.join(self.save_dir, k + "_degDif.tsv"), sep='\t', index=True)
+        return pairwise

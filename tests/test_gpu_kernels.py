@@ -1,0 +1,181 @@
+"""GPU parity tests: every call goes through the C ABI (libn2v2r_b200.so) and is checked against
+the CPU oracle (oracle/reference_port.py) or the golden vectors generated from the reference."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from oracle import reference_port as port
+
+
+def _t(a, gpu):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(gpu)
+
+
+# ---- K0 ---------------------------------------------------------------------------------------
+@pytest.mark.parametrize("weighted", [False, True])
+def test_sbm_generator_matches_numpy_twin(gpu, weighted):
+    from node2vec2rank_b200 import device as D
+    from node2vec2rank_b200.synthetic import block_matrices, sbm_layer_numpy
+    n, K = 517, 7
+    Bs, _ = block_matrices(K, 2, seed=3)
+    for t in range(2):
+        got = D.sbm_generate(n, K, Bs[t], seed=11, layer=t, weighted=weighted).cpu().numpy()
+        ref = sbm_layer_numpy(n, K, Bs[t], 11, t, weighted)
+        assert np.array_equal(got, ref)
+        assert np.array_equal(got, got.T) and not got.diagonal().any()
+
+
+# ---- K1 -----------------------------------------------------------------------------------------
+def test_network_transform_golden_bit_exact(gpu, golden_dir):
+    from node2vec2rank_b200.preprocessing_utils import network_transform
+    z = np.load(os.path.join(golden_dir, "network_transform.npz"))
+    meta = json.load(open(os.path.join(golden_dir, "network_transform.json")))
+    for i, m in enumerate(meta):
+        x = z[f"in_{i}"]
+        before = x.copy()
+        fl = dict(m["flags"])
+        projected = x.shape[0] != x.shape[1]
+        out = network_transform(x, **fl)
+        assert np.array_equal(before, x)
+        assert out.dtype == np.float32 and out.shape == z[f"out_{i}"].shape
+        if projected:       # fp64 dgemm vs split-bf16 tensor-core GEMM: fp32-level agreement, same support
+            ref = z[f"out_{i}"]
+            assert np.allclose(out, ref, rtol=2e-6, atol=1e-6), (i, m)
+        else:
+            assert np.array_equal(out, z[f"out_{i}"]), (i, m)
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+@pytest.mark.parametrize("keep", [100, 50, 10, 1, 0.5])
+def test_percentile_cut_matches_numpy(gpu, dtype, keep):
+    from node2vec2rank_b200 import device as D
+    rng = np.random.default_rng(5)
+    x = rng.normal(size=(301, 301)).astype(dtype)
+    x[rng.random(x.shape) < 0.4] = 0
+    x[:20] = np.round(x[:20], 1)                     # ties
+    for absolute, thr in [(False, None), (True, None), (True, 0.3), (False, 0.1)]:
+        y = np.abs(x) if absolute else x.copy()
+        if thr is not None:
+            y[y < thr] = 0
+        ref = np.percentile(y[y.nonzero()], 100 - keep)
+        got = D.percentile_cut(_t(x, gpu), 100 - keep, absolute, thr)
+        assert got == ref and type(got) == type(ref), (dtype, keep, absolute, thr, got, ref)
+
+
+def test_transform_planes_colsum_and_symmetry(gpu):
+    from node2vec2rank_b200 import device as D
+    rng = np.random.default_rng(9)
+    n = 333
+    x = rng.random((n, n)).astype(np.float32)
+    x = (x + x.T) / 2
+    x[x < 0.5] = 0
+    L = D.make_layer(_t(x, gpu))
+    assert L.n_planes == 3 and L.symmetric and L.planes_t is None
+    assert np.array_equal(L.numpy(), x)
+    assert np.allclose(L.colsum.cpu().numpy(), x.astype(np.float64).sum(0), rtol=1e-12)
+    b = (x != 0).astype(np.float32)
+    Lb = D.make_layer(_t(b, gpu))
+    assert Lb.n_planes == 1 and np.array_equal(Lb.numpy(), b)
+    a = np.triu(x)
+    La = D.make_layer(_t(a, gpu))
+    assert not La.symmetric and La.planes_t is not None
+    assert np.array_equal(La.planes_t[:, :, :n].float().sum(0).cpu().numpy(), a.T)
+
+
+# ---- K3/K4 ----------------------------------------------------------------------------------------
+@pytest.mark.parametrize("n,l,planes", [(1000, 64, 1), (777, 32, 3), (2048, 48, 2), (4500, 64, 1), (300, 16, 3), (1030, 80, 1)])
+def test_layer_apply_tcgen05_vs_fp64(gpu, n, l, planes):
+    from node2vec2rank_b200 import _native as N
+    from node2vec2rank_b200 import device as D
+    rng = np.random.default_rng(n + l)
+    if planes == 1:
+        a = (rng.random((n, n)) < 0.2).astype(np.float32)
+    elif planes == 2:
+        a = (rng.integers(0, 65536, size=(n, n)).astype(np.float32) / 65536.0) * (rng.random((n, n)) < 0.3)
+        a = a.astype(np.float32)
+    else:
+        a = (rng.random((n, n)).astype(np.float32)) * (rng.random((n, n)) < 0.3).astype(np.float32)
+    L = D.make_layer(_t(a, gpu))
+    assert L.n_planes == planes
+    x = rng.normal(size=(n, l)).astype(np.float32)
+    xd = _t(x, gpu)
+    for transpose in (False, True):
+        ref = (a.T if transpose else a).astype(np.float64) @ x.astype(np.float64)
+        scale = np.abs(ref).max()
+        simt = D.layer_apply(L, xd, transpose, algo=N.ALGO_SIMT).cpu().numpy()
+        assert np.abs(simt - ref).max() <= 2e-6 * scale
+        for k_chunk in (0, 512):
+            got = D.layer_apply(L, xd, transpose, algo=N.ALGO_TCGEN05, k_chunk=k_chunk).cpu().numpy()
+            err = np.abs(got - ref).max() / scale
+            assert err <= 2e-6, (n, l, planes, transpose, k_chunk, err)   # fp32-level: operands carry 24 bits, fp32 accumulate
+
+
+# ---- K9-K11 ----------------------------------------------------------------------------------------
+def test_distances_golden(gpu, golden_dir):
+    from node2vec2rank_b200.model_utils import compute_pairwise_distances
+    z = np.load(os.path.join(golden_dir, "distances.npz"))
+    for metric in ("euclidean", "cosine", "correlation"):
+        for d in (2, 4, 9, 24):
+            got = np.asarray(compute_pairwise_distances(z["E1"][:, :d], z["E2"][:, :d], metric))
+            ref = z[f"{metric}_{d}"]
+            assert np.array_equal(np.isnan(got), np.isnan(ref))
+            assert np.allclose(got, ref, rtol=1e-12, atol=1e-15, equal_nan=True), (metric, d)
+    with pytest.raises(NotImplementedError):
+        compute_pairwise_distances(z["E1"], z["E2"], "manhattan")
+
+
+@pytest.mark.parametrize("strategy", ["sequential", "one_vs_before", "one_vs_rest"])
+def test_distance_strategies_vs_oracle(gpu, strategy):
+    from node2vec2rank_b200 import _native as N
+    from node2vec2rank_b200 import device as D
+    rng = np.random.default_rng(2)
+    T, n, k = 4, 257, 24
+    emb = rng.normal(size=(T, n, k)).astype(np.float32)
+    emb[2, 7] = 0
+    dims = [1, 2, 4, 13, 24]
+    mets = ["euclidean", "cosine", "correlation"]
+    names, cd, cm = D.column_specs(dims, mets)
+    got = D.distances(_t(emb, gpu), cd, cm, N.STRATEGIES[strategy]).cpu().numpy()
+    ref = port.rank_columns(emb.astype(np.float64), dims, mets, strategy)
+    assert got.shape[0] == len(ref)
+    for c, key in enumerate(sorted(ref, key=int)):
+        rn, rs = ref[key]
+        assert rn == names
+        assert np.allclose(got[c].T, rs, rtol=1e-11, atol=1e-14, equal_nan=True), (strategy, key)
+
+
+def test_rank_borda_golden_and_ties(gpu, golden_dir):
+    from node2vec2rank_b200 import device as D
+    z = np.load(os.path.join(golden_dir, "borda.npz"))
+    b, _ = D.rank_borda(_t(z["scores"].T, gpu))
+    assert np.array_equal(b.cpu().numpy(), z["borda"])
+    rng = np.random.default_rng(4)
+    for n, cols in [(1, 3), (2, 1), (1000, 22), (5003, 7), (70000, 3)]:
+        s = rng.normal(size=(n, cols))
+        s[rng.random(s.shape) < 0.2] = 0.5          # heavy ties
+        s[rng.random(s.shape) < 0.05] = np.nan
+        s[rng.random(s.shape) < 0.02] = -0.0
+        s[rng.random(s.shape) < 0.02] = 0.0
+        s[rng.random(s.shape) < 0.01] = np.inf
+        s[rng.random(s.shape) < 0.01] = -np.inf
+        borda, pos = D.rank_borda(_t(s.T, gpu), want_positions=True)
+        ref_pos = np.stack([port.descending_positions(s[:, c]) for c in range(cols)])
+        assert np.array_equal(pos.cpu().numpy(), ref_pos), (n, cols)
+        assert np.array_equal(borda.cpu().numpy(), port.borda_from_scores(s))
+        assert borda.sum().item() == cols * n * (n + 1) // 2
+
+
+def test_borda_aggregate_parallel_mirror(gpu):
+    from node2vec2rank_b200.model_utils import borda_aggregate_parallel
+    rng = np.random.default_rng(8)
+    names = [f"g{i}" for i in range(300)]
+    lists = [list(rng.permutation(names)) for _ in range(5)]
+    got = borda_aggregate_parallel(lists)
+    idx, ref = port.borda_aggregate(lists, faithful=False)
+    assert list(got.index) == idx and list(got.columns) == ["borda_ranks"]
+    assert got["borda_ranks"].dtype == np.int64 and np.array_equal(got["borda_ranks"].to_numpy(), ref)
