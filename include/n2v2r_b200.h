@@ -121,7 +121,7 @@ int n2v2r_project(void* stream, const void* d_W, int dtype, int64_t rows, int64_
  * K3-K8  UASE: truncated SVD of the unfolded matrix [A_1 | ... | A_T] and the per-layer
  * right embeddings V_t * S^(1/2).  Replaces spectral_embedding.UASE as called at
  * model.py:54-55 (scipy svds / ARPACK underneath).
- * Randomised block subspace iteration with Rayleigh-Ritz and optional Chebyshev filter;
+ * Chebyshev-filtered block subspace iteration with Rayleigh-Ritz, locking and deflation;
  * CholeskyQR2; single-CTA Jacobi for the l x l eigenproblem; the only O(n^2) work is the
  * streaming skinny products Y += A_t X and Z_t = A_t^T Q.
  * Layer sharding: this process owns T_local layers [layer_offset, layer_offset+T_local)
@@ -143,7 +143,8 @@ typedef struct {
   int32_t l;               /* block width: 16, 32, 48, 64 or 80                          */
   int32_t max_iters;       /* cap on operator applications (A A^T)                       */
   int32_t min_iters;
-  int32_t cheb_degree;     /* 1 = plain subspace iteration; m>1 = degree-m Chebyshev filter */
+  int32_t cheb_degree;     /* cap on the Chebyshev filter degree per outer iteration (0 = default 32,
+                              1 = plain subspace iteration)                                */
   int32_t algo;            /* n2v2r_algo_t                                               */
   int32_t k_chunk;         /* columns of A per accumulation unit (0 = default)           */
   int32_t n_check;         /* number of entries of h_check_dims                          */
@@ -153,15 +154,20 @@ typedef struct {
 } n2v2r_uase_params_t;
 
 typedef struct {
-  int32_t iterations;      /* operator applications done                                 */
+  int32_t iterations;      /* applications of the operator A A^T to the l-column block      */
   int32_t layer_passes;    /* number of (layer x skinny product) launches                */
-  int32_t converged;
+  int32_t converged;       /* 0 no, 1 yes, 2 residuals stagnated at the fp32 floor          */
   int32_t kernel_launches;
-  double stream_ms;        /* CUDA-event time spent in the streaming kernels             */
+  int32_t outer_iterations;/* Rayleigh-Ritz steps                                           */
+  int32_t locked;          /* Ritz pairs at the residual floor when the solver stopped      */
+  double stream_ms;        /* CUDA-event time of the streaming products (split + MMA + reduce) */
+  double mma_ms;           /* CUDA-event time of the tcgen05 MMA kernel launches alone      */
+  int32_t mma_launches;
+  int32_t reserved;
   double total_ms;
   double stream_bytes;     /* algorithmic bytes of those launches            */
   double max_angle_bound;  /* final value of the stopping quantity                       */
-  double resid[96];        /* final relative residual per Ritz pair                      */
+  double resid[96];        /* final residual norm per Ritz pair, relative to lambda_1       */
   double ritz[96];         /* Ritz values (sigma^2), descending                          */
 } n2v2r_uase_stats_t;
 

@@ -41,7 +41,9 @@ class UaseParams(C.Structure):
 
 class UaseStats(C.Structure):
     _fields_ = [("iterations", C.c_int32), ("layer_passes", C.c_int32), ("converged", C.c_int32),
-                ("kernel_launches", C.c_int32), ("stream_ms", C.c_double), ("total_ms", C.c_double),
+                ("kernel_launches", C.c_int32), ("outer_iterations", C.c_int32), ("locked", C.c_int32),
+                ("stream_ms", C.c_double), ("mma_ms", C.c_double), ("mma_launches", C.c_int32), ("reserved", C.c_int32),
+                ("total_ms", C.c_double),
                 ("stream_bytes", C.c_double), ("max_angle_bound", C.c_double),
                 ("resid", C.c_double * 96), ("ritz", C.c_double * 96)]
 

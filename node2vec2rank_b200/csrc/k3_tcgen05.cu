@@ -12,6 +12,7 @@
 #include "k5_orth.cuh"
 #include <cuda.h>
 #include <cudaTypedefs.h>
+#include <vector>
 
 namespace n2v2r {
 
@@ -295,6 +296,11 @@ __global__ void __launch_bounds__(256) split_planes_kernel(const T* __restrict__
 }
 
 // ---- host ---------------------------------------------------------------------------------------
+// Optional per-launch timing of the MMA kernel alone (roofline evidence): event pairs are appended to
+// the sink when one is installed by the caller (uase solver / layer_apply).
+static thread_local std::vector<cudaEvent_t>* g_mma_events = nullptr;
+void set_mma_event_sink(std::vector<cudaEvent_t>* sink) { g_mma_events = sink; }
+
 static PFN_cuTensorMapEncodeTiled_v12000 get_encode() {
   static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
   if (!fn) {
@@ -371,8 +377,19 @@ static int launch_mma(cudaStream_t s, const void* a_planes, int n_planes, int64_
   const size_t smem = (size_t)a.stages * a.stage_bytes + 1024;
   const int n_units = a.n_tiles * a.n_splits * a.n_jb;
   const int grid = n_units < sm_count() ? n_units : sm_count();
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (g_mma_events) {
+    N2V2R_CUDA(cudaEventCreate(&e0));
+    N2V2R_CUDA(cudaEventCreate(&e1));
+    N2V2R_CUDA(cudaEventRecord(e0, s));
+  }
   stream_mma_kernel<<<grid, 192, smem, s>>>(mA[0], mA[1], mA[2], mX, a);
   N2V2R_CHECK_LAUNCH();
+  if (g_mma_events) {
+    N2V2R_CUDA(cudaEventRecord(e1, s));
+    g_mma_events->push_back(e0);
+    g_mma_events->push_back(e1);
+  }
   return N2V2R_OK;
 }
 

@@ -227,6 +227,7 @@ __global__ void __launch_bounds__(512) smallmat_kernel(int mode, int l, const do
     for (int e = tid; e < ll; e += nt) gW[e] = B[e];
     for (int i = tid; i < l; i += nt) gLam[i] = lam[i];
     __syncthreads();
+    if (mode == 0 && gS == nullptr) return;               // Rayleigh-Ritz only: W, lam
     if (mode == 2) {
       for (int e = tid; e < ll; e += nt) {
         const int j = e % l;
@@ -338,6 +339,30 @@ __global__ void __launch_bounds__(128) apply_small_kernel(const float* __restric
   }
 }
 
+// ---- deflation: X[n][l] -= U[n][:p] * G[:p][l]  (U = locked Ritz vectors, G = U^T X, fp64) ------
+__global__ void __launch_bounds__(256) sub_proj_kernel(float* __restrict__ X, const float* __restrict__ U, int64_t n, int l,
+                                                       int p, const double* __restrict__ G) {
+  extern __shared__ double sg[];            // p * l
+  float* su = (float*)(sg + (size_t)p * l); // 32 * p
+  for (int e = threadIdx.x; e < p * l; e += 256) sg[e] = G[e];
+  for (int64_t rb = (int64_t)blockIdx.x * 32; rb < n; rb += (int64_t)gridDim.x * 32) {
+    __syncthreads();
+    for (int e = threadIdx.x; e < 32 * p; e += 256) {
+      const int r = e / p, q = e - r * p;
+      su[e] = (rb + r < n) ? U[(rb + r) * l + q] : 0.f;
+    }
+    __syncthreads();
+    for (int e = threadIdx.x; e < 32 * l; e += 256) {
+      const int r = e / l, j = e - r * l;
+      if (rb + r < n) {
+        double s = 0.0;
+        for (int q = 0; q < p; ++q) s += (double)su[r * p + q] * sg[q * l + j];
+        X[(rb + r) * l + j] = (float)((double)X[(rb + r) * l + j] - s);
+      }
+    }
+  }
+}
+
 // ---- split-transpose: X fp32 [n][l] -> Xs bf16 [3][l][n_pad] (K-major operand of the MMA) ----
 __global__ void __launch_bounds__(256) split_transpose_kernel(const float* __restrict__ X, int64_t n, int l, int64_t n_pad,
                                                               __nv_bfloat16* __restrict__ Xs) {
@@ -430,6 +455,21 @@ int launch_apply_small(cudaStream_t s, const float* X, int64_t n, int l, const d
   apply_small_kernel<<<grid, 128, smem, s>>>(X, n, l, C, ldc, lo, Out, ld_out, Qm, W, lam, resid_partials, tiles_per_cta);
   N2V2R_CHECK_LAUNCH();
   if (n_parts) *n_parts = grid;
+  return N2V2R_OK;
+}
+
+int launch_sub_proj(cudaStream_t s, float* X, const float* U, int64_t n, int l, int p, const double* G) {
+  if (p <= 0) return N2V2R_OK;
+  static bool done = false;
+  const size_t max_smem = sizeof(double) * kMaxL * kMaxL + sizeof(float) * 32 * kMaxL;
+  if (!done) {
+    N2V2R_CUDA(cudaFuncSetAttribute(sub_proj_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)max_smem));
+    done = true;
+  }
+  const int64_t tiles = (n + 31) / 32;
+  const int grid = (int)(tiles < (int64_t)sm_count() * 4 ? tiles : (int64_t)sm_count() * 4);
+  sub_proj_kernel<<<grid, 256, sizeof(double) * p * l + sizeof(float) * 32 * p, s>>>(X, U, n, l, p, G);
+  N2V2R_CHECK_LAUNCH();
   return N2V2R_OK;
 }
 

@@ -2,6 +2,7 @@
 // (k3_stream.cu), shared with the solver (uase_solver.cu).
 #pragma once
 #include "common.cuh"
+#include <vector>
 
 namespace n2v2r {
 
@@ -17,6 +18,8 @@ int launch_smallmat(cudaStream_t s, int mode, int l, const double* H, const doub
 // Out[n][lo] = X[n][l] C[l][lo]; optional residual partials ||Y W - Q W Lam||^2 (X plays Y)
 int launch_apply_small(cudaStream_t s, const float* X, int64_t n, int l, const double* C, int ldc, int lo, float* Out, int64_t ld_out,
                        const float* Qm, const double* W, const double* lam, double* resid_partials, int* n_parts);
+// X -= U[:, :p] G[:p, :]  (deflation against the p locked Ritz vectors)
+int launch_sub_proj(cudaStream_t s, float* X, const float* U, int64_t n, int l, int p, const double* G);
 int launch_sum_partials(cudaStream_t s, const double* partials, int n_parts, int count, double* out);
 int launch_split_transpose(cudaStream_t s, const float* X, int64_t n, int l, int64_t n_pad, __nv_bfloat16* Xs);
 int launch_random_block(cudaStream_t s, float* X, int64_t n, int l, uint64_t seed);
@@ -29,6 +32,7 @@ struct StreamPlan {
   int l, algo, k_chunk, n_splits;
   size_t xs_bytes, part_bytes;     // split-transposed operand, K-split partial sums
 };
+void set_mma_event_sink(std::vector<cudaEvent_t>* sink);   // k3_tcgen05.cu: time every MMA launch (nullptr = off)
 int make_stream_plan(int64_t n, int l, int algo, int k_chunk, StreamPlan* plan);
 // out[n][l] (= or +=) A X (transpose=0) / A^T X (transpose=1).  x: fp32 [n][l].
 // xs / parts: scratch sized by the plan (may be null for the SIMT algo).

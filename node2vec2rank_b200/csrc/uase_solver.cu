@@ -1,18 +1,24 @@
-// UASE solver: randomised block subspace iteration with Rayleigh-Ritz on M = A A^T,
-// A = [A_1 | ... | A_T].  Replaces spectral_embedding.UASE (model.py:54-55), i.e. scipy
-// svds/ARPACK (_svds.py:428-535) + the sqrt(sigma) scaling of the right vectors.
+// UASE solver: Chebyshev-filtered block subspace iteration with Rayleigh-Ritz, locking and
+// deflation on M = A A^T, A = [A_1 | ... | A_T].  Replaces spectral_embedding.UASE
+// (model.py:54-55), i.e. scipy svds/ARPACK (_svds.py:428-535) + the sqrt(sigma) scaling.
 //
-// Per iteration (Q n x l orthonormal, replicated on every rank):
-//   Z_t = A_t^T Q  (local layers)          -- streaming product, K4
-//   Y   = sum_t A_t Z_t  (+ all-reduce)     -- streaming product, K3      => Y = M Q
-//   H = Q^T Y, S = Y^T Y                    -- K5 (fp64 accumulate)
-//   (W, Lam) = eig(H); C = W chol(W^T S W)^-1 -- K7 Jacobi + K6 Cholesky, one CTA
-//   residuals ||Y w_j - lam_j Q w_j||, Q <- Y C, second CholeskyQR pass
-// Stop: for every swept d, sqrt(sum_{j<=d} r_j^2) / (lam_d - lam_{d+1}) <= tol  (Davis-Kahan
-// bound on the sine of the subspace angle), or the bound stagnates (fp32 floor), or max_iters.
-// Final: G = sum_t Z_t^T Z_t (all-reduce) = W Sigma^2 W^T; embedding_t = Z_t W Sigma^-1/2.
+// Outer iteration (Q n x l orthonormal, replicated on every rank):
+//   Z_t = A_t^T Q (local layers), Y = sum_t A_t Z_t (+ all-reduce)   -- streaming products K4/K3
+//   H = Q^T Y -> (W, Lam) = eig(H)                                   -- K5 + K7 (one-CTA Jacobi, fp64)
+//   Ritz vectors Qw = Q W, Yw = Y W, residuals r_j = ||Yw_j - lam_j Qw_j||
+//   host: lock the leading Ritz pairs at the residual floor, test convergence, pick the degree m
+//   degree-m Chebyshev filter (three-term recurrence, interval [0, lam_l] damped, scaled at the
+//   largest unlocked Ritz value), every step deflated against the locked vectors:
+//       X_{j+1} = (2 s_{j+1}/e)(M X_j - c X_j) - s_j s_{j+1} X_{j-1}
+//   Q <- CholeskyQR2([locked | filtered])                            -- K5 + K6
+// Stop: Davis-Kahan bound sqrt(sum_{j<=d} r_j^2)/(lam_d - lam_{d+1}) <= tol at every swept d, or
+// every wanted residual r_j <= max(8 eps32 lam_j, 0.02 eps32 lam_1) (the measured fp32 floor is ~eps32 lam_j),
+// or the residuals stagnate, or max_iters applications.
+// Final: embedding_t = Z_t W Sigma^-1/2 (= V_t Sigma^1/2) from the last Rayleigh-Ritz application.
 #include "k5_orth.cuh"
+#include <float.h>
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 #include <vector>
 #include <algorithm>
@@ -20,7 +26,7 @@
 namespace n2v2r {
 
 struct SolverBufs {
-  float *Q, *Y, *Qn;
+  float *Q, *Y, *Qn, *Qw, *X0, *X1, *X2, *Zt;
   float* Z;                 // T_local * n * l
   __nv_bfloat16* xs;
   float* parts;
@@ -35,6 +41,11 @@ static size_t carve(const n2v2r_uase_params_t* p, const StreamPlan& plan, void* 
   b->Q = a.take<float>(nl);
   b->Y = a.take<float>(nl);
   b->Qn = a.take<float>(nl);
+  b->Qw = a.take<float>(nl);
+  b->X0 = a.take<float>(nl);
+  b->X1 = a.take<float>(nl);
+  b->X2 = a.take<float>(nl);
+  b->Zt = a.take<float>(nl);
   b->Z = a.take<float>(nl * (size_t)p->T_local);
   b->xs = a.take<__nv_bfloat16>(plan.xs_bytes / sizeof(__nv_bfloat16));
   b->parts = a.take<float>(plan.part_bytes / sizeof(float));
@@ -71,6 +82,8 @@ extern "C" size_t n2v2r_uase_workspace_bytes(const n2v2r_uase_params_t* p) {
 
 #define RC(call) do { int _rc = (call); if (_rc != N2V2R_OK) return _rc; } while (0)
 
+static double cheb_T(double x, int m) { return cosh((double)m * acosh(x > 1.0 ? x : 1.0)); }
+
 extern "C" int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2r_layer_t* L, void* d_ws, size_t ws_bytes,
                           n2v2r_allreduce_fn allreduce, void* user, float* d_embed, float* d_left, double* h_sigma,
                           n2v2r_uase_stats_t* st) {
@@ -85,20 +98,57 @@ extern "C" int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2
   const int64_t n = p->n;
   const int l = p->l, k = p->k, T = p->T_local;
   const size_t nl = (size_t)n * l;
+  const int m_cap = p->cheb_degree <= 0 ? 32 : p->cheb_degree;
+  double floor_mult = 0.02, rel_floor = 8.0 * (double)FLT_EPSILON;   // residual target: 8 eps32 lam_j (measured fp32 floor ~ eps32 lam_j)
+  if (const char* ev = getenv("N2V2R_FLOOR_MULT")) floor_mult = atof(ev);     // developer knobs (scripts/probe_solver.py)
+  if (const char* ev = getenv("N2V2R_REL_FLOOR")) rel_floor = atof(ev);
+  const double rho_max = 1e4;            // cap on T_m(x_unlocked)/T_m(x_k): keeps every fp32 column dominated by its own Ritz vector
   n2v2r_uase_stats_t stats;
   memset(&stats, 0, sizeof(stats));
   cudaEvent_t ev_all0, ev_all1;
   N2V2R_CUDA(cudaEventCreate(&ev_all0));
   N2V2R_CUDA(cudaEventCreate(&ev_all1));
-  std::vector<cudaEvent_t> evs;
+  std::vector<cudaEvent_t> evs, mma_evs;
+  struct SinkGuard { SinkGuard(std::vector<cudaEvent_t>* v) { set_mma_event_sink(v); } ~SinkGuard() { set_mma_event_sink(nullptr); } }
+      sink_guard(p->algo == N2V2R_ALGO_TCGEN05 ? &mma_evs : nullptr);
   N2V2R_CUDA(cudaEventRecord(ev_all0, s));
+  const int per_pass = (p->algo == N2V2R_ALGO_TCGEN05 ? 3 : 1);
 
-  // CholeskyQR2 of the buffer X -> orthonormal, result in `dst` (tmp is scratch)
+  // one pass of CholeskyQR: dst = X chol(X^T X)^-1
   auto cholqr_pass = [&](const float* X, float* dst) -> int {
     RC(launch_xty(s, X, X, n, l, b.partials, kMaxParts, b.G, 0));
     RC(launch_smallmat(s, 1, l, b.G, nullptr, nullptr, nullptr, b.C, nullptr, b.flag));
     RC(launch_apply_small(s, X, n, l, b.C, l, l, dst, l, nullptr, nullptr, nullptr, nullptr, nullptr));
     stats.kernel_launches += 4;
+    return N2V2R_OK;
+  };
+  // out = M x = sum_t A_t (A_t^T x) (+ all-reduce).  keep_z: Z_t kept per layer (Rayleigh-Ritz application)
+  auto apply_M = [&](const float* x, float* out, bool keep_z) -> int {
+    cudaEvent_t e0, e1;
+    N2V2R_CUDA(cudaEventCreate(&e0));
+    N2V2R_CUDA(cudaEventCreate(&e1));
+    N2V2R_CUDA(cudaEventRecord(e0, s));
+    for (int t = 0; t < T; ++t) {
+      float* z = keep_z ? b.Z + t * nl : b.Zt;
+      RC(stream_apply(s, plan, L[t], 1, x, b.xs, b.parts, z, 0, &stats.stream_bytes));       // Z_t = A_t^T x
+      RC(stream_apply(s, plan, L[t], 0, z, b.xs, b.parts, out, t > 0, &stats.stream_bytes));  // out += A_t Z_t
+    }
+    N2V2R_CUDA(cudaEventRecord(e1, s));
+    evs.push_back(e0); evs.push_back(e1);
+    stats.layer_passes += 2 * T;
+    stats.kernel_launches += 2 * T * per_pass;
+    stats.iterations += 1;
+    if (allreduce && allreduce(user, out, (int64_t)nl, N2V2R_F32, stream) != 0) {
+      set_error("uase: all-reduce callback failed (Y)");
+      return N2V2R_ECOMM;
+    }
+    return N2V2R_OK;
+  };
+  auto deflate = [&](float* X, int locked) -> int {
+    if (locked <= 0) return N2V2R_OK;
+    RC(launch_xty(s, b.Qw, X, n, l, b.partials, kMaxParts, b.G, 0));     // rows < locked of Qw^T X are used
+    RC(launch_sub_proj(s, X, b.Qw, n, l, locked, b.G));
+    stats.kernel_launches += 3;
     return N2V2R_OK;
   };
 
@@ -107,49 +157,35 @@ extern "C" int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2
   RC(cholqr_pass(b.Qn, b.Q));
   stats.kernel_launches += 1;
 
-  std::vector<double> lam(l), res(l), hist;
-  double bound = INFINITY, best = INFINITY;
-  int since_best = 0;
-  int it = 0;
-  bool converged = false, stagnated = false;
+  std::vector<double> lam(l), res(l);
+  double bound = INFINITY;
+  int locked = 0, outer = 0, stalls = 0;
+  bool converged = false, stagnated = false, last_filtered = false;
+  double best_worst = INFINITY;
   while (true) {
-    ++it;
-    cudaEvent_t e0, e1;
-    N2V2R_CUDA(cudaEventCreate(&e0));
-    N2V2R_CUDA(cudaEventCreate(&e1));
-    N2V2R_CUDA(cudaEventRecord(e0, s));
-    for (int t = 0; t < T; ++t)                                   // Z_t = A_t^T Q
-      RC(stream_apply(s, plan, L[t], 1, b.Q, b.xs, b.parts, b.Z + t * nl, 0, &stats.stream_bytes));
-    for (int t = 0; t < T; ++t)                                   // Y = sum_t A_t Z_t
-      RC(stream_apply(s, plan, L[t], 0, b.Z + t * nl, b.xs, b.parts, b.Y, t > 0, &stats.stream_bytes));
-    N2V2R_CUDA(cudaEventRecord(e1, s));
-    evs.push_back(e0); evs.push_back(e1);
-    stats.layer_passes += 2 * T;
-    stats.kernel_launches += 2 * T * (p->algo == N2V2R_ALGO_TCGEN05 ? 3 : 1);
-    if (allreduce && allreduce(user, b.Y, (int64_t)nl, N2V2R_F32, stream) != 0) {
-      set_error("uase: all-reduce callback failed (Y)");
-      return N2V2R_ECOMM;
-    }
-    // Rayleigh-Ritz on span(Q) with Y = M Q
+    ++outer;
+    RC(apply_M(b.Q, b.Y, true));
+    // Rayleigh-Ritz on span(Q): H = Q^T M Q
     RC(launch_xty(s, b.Q, b.Y, n, l, b.partials, kMaxParts, b.H, 0));
-    RC(launch_xty(s, b.Y, b.Y, n, l, b.partials, kMaxParts, b.S, 0));
-    RC(launch_smallmat(s, 0, l, b.H, b.S, b.W, b.lam, b.C, nullptr, b.flag));
+    RC(launch_smallmat(s, 0, l, b.H, nullptr, b.W, b.lam, nullptr, nullptr, b.flag));
     int n_parts = 0;
-    RC(launch_apply_small(s, b.Y, n, l, b.C, l, l, b.Qn, l, b.Q, b.W, b.lam, b.rpart, &n_parts));
+    RC(launch_apply_small(s, b.Y, n, l, b.W, l, l, b.X1, l, b.Q, b.W, b.lam, b.rpart, &n_parts));   // X1 = Yw, residuals
     RC(launch_sum_partials(s, b.rpart, n_parts, l, b.resid));
-    stats.kernel_launches += 7;
+    RC(launch_apply_small(s, b.Q, n, l, b.W, l, l, b.Qw, l, nullptr, nullptr, nullptr, nullptr, nullptr));  // Qw = Q W
+    stats.kernel_launches += 6;
     N2V2R_CUDA(cudaMemcpyAsync(lam.data(), b.lam, sizeof(double) * l, cudaMemcpyDeviceToHost, s));
     N2V2R_CUDA(cudaMemcpyAsync(res.data(), b.resid, sizeof(double) * l, cudaMemcpyDeviceToHost, s));
     N2V2R_CUDA(cudaStreamSynchronize(s));
-    // stopping quantity
-    bound = 0.0;
+    for (int j = 0; j < l; ++j) res[j] = sqrt(std::max(res[j], 0.0));    // residual norms
+    // ---- host decisions --------------------------------------------------------------------
     auto angle_bound = [&](int d) -> double {
       double r2 = 0.0;
-      for (int j = 0; j < d && j < l; ++j) r2 += res[j];
+      for (int j = 0; j < d && j < l; ++j) r2 += res[j] * res[j];
       const double gap = (d < l) ? lam[d - 1] - lam[d] : lam[d - 1];
       if (!(gap > 0.0)) return INFINITY;
       return sqrt(r2) / gap;
     };
+    bound = 0.0;
     if (p->h_check_dims && p->n_check > 0) {
       for (int c = 0; c < p->n_check; ++c) {
         const int d = p->h_check_dims[c];
@@ -158,24 +194,70 @@ extern "C" int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2
     } else {
       bound = angle_bound(k);
     }
-    if (bound < best * 0.9) { best = bound; since_best = 0; } else { ++since_best; }
-    converged = bound <= p->tol;
-    stagnated = since_best >= 12 && it >= p->min_iters;
-    if ((converged && it >= p->min_iters) || stagnated || it >= p->max_iters) break;
-    RC(cholqr_pass(b.Qn, b.Q));                                   // second CholeskyQR pass -> next Q
+    const double floor_ = floor_mult * (double)FLT_EPSILON * std::max(lam[0], 0.0);
+    auto target = [&](int j) { return std::max(floor_, rel_floor * lam[j]); };
+    auto at_floor = [&](int j) { return res[j] <= target(j); };
+    locked = 0;
+    while (locked < k && at_floor(locked)) ++locked;
+    bool all_floor = true;
+    for (int j = 0; j < k; ++j) all_floor = all_floor && at_floor(j);
+    // stagnation: two filtered outer iterations in a row without a 30 % drop of the worst residual ratio
+    double worst = 0.0;
+    for (int j = 0; j < k; ++j) worst = std::max(worst, res[j] / target(j));
+    if (last_filtered && worst > 0.7 * best_worst) ++stalls; else if (worst <= 0.7 * best_worst) stalls = 0;
+    best_worst = std::min(best_worst, worst);
+    stagnated = stalls >= 2;
+    converged = (bound <= p->tol) || all_floor || stagnated;
+    last_filtered = false;
+    if ((converged && stats.iterations >= p->min_iters) || stats.iterations >= p->max_iters) break;
+    // ---- filter degree ----------------------------------------------------------------------
+    const double hi = std::max(lam[l - 1], 0.0);           // damp [0, lam_l]
+    const double c = 0.5 * hi, e = 0.5 * hi;
+    const double lam_u = lam[locked < k ? locked : k - 1];   // largest unlocked Ritz value
+    int m = 1;
+    if (m_cap > 1 && e > 0.0 && lam[k - 1] > hi) {
+      const double xu = (lam_u - c) / e, xk = (lam[k - 1] - c) / e;
+      while (m < m_cap && cheb_T(xu, m + 1) / cheb_T(xk, m + 1) <= rho_max) ++m;
+      const double need = ceil(log(4.0 * std::max(worst, 1.0)) / acosh(xk)) + 1.0;   // degree that would reach the targets
+      if (m > 1) m = std::max(2, std::min(m, (int)std::min(need, 1e6)));
+      m = std::min(m, p->max_iters - stats.iterations);
+    }
+    if (m <= 1) {                                            // plain subspace step: Q <- orth(M Qw)
+      RC(cholqr_pass(b.X1, b.Qn));
+      RC(cholqr_pass(b.Qn, b.Q));
+      continue;
+    }
+    last_filtered = true;
+    // X0 = Qw, X1 = (s1/e)(Yw - c Qw), then the three-term recurrence
+    const double s1 = e / (lam_u - c);
+    double sg = s1;
+    N2V2R_CUDA(cudaMemcpyAsync(b.X0, b.Qw, sizeof(float) * nl, cudaMemcpyDeviceToDevice, s));
+    RC(launch_axpbypcz(s, b.X1, b.X1, s1 / e, b.Qw, -c * s1 / e, nullptr, 0.0, (int64_t)nl));
+    stats.kernel_launches += 2;
+    float *x0 = b.X0, *x1 = b.X1, *x2 = b.X2;
+    for (int j = 2; j <= m; ++j) {
+      RC(deflate(x1, locked));
+      RC(apply_M(x1, b.Y, false));
+      const double s2 = 1.0 / (2.0 / s1 - sg);
+      RC(launch_axpbypcz(s, x2, b.Y, 2.0 * s2 / e, x1, -2.0 * s2 * c / e, x0, -sg * s2, (int64_t)nl));
+      stats.kernel_launches += 1;
+      float* t = x0; x0 = x1; x1 = x2; x2 = t;
+      sg = s2;
+    }
+    if (locked > 0) {
+      RC(deflate(x1, locked));
+      N2V2R_CUDA(cudaMemcpy2DAsync(x1, sizeof(float) * l, b.Qw, sizeof(float) * l, sizeof(float) * locked, (size_t)n,
+                                   cudaMemcpyDeviceToDevice, s));
+    }
+    RC(cholqr_pass(x1, b.Qn));
+    RC(cholqr_pass(b.Qn, b.Q));
   }
-  // final Rayleigh-Ritz through the right factor: G = sum_t Z_t^T Z_t = Q^T M Q
-  for (int t = 0; t < T; ++t) RC(launch_xty(s, b.Z + t * nl, b.Z + t * nl, n, l, b.partials, kMaxParts, b.G, t > 0));
-  if (allreduce && allreduce(user, b.G, (int64_t)l * l, N2V2R_F64, stream) != 0) {
-    set_error("uase: all-reduce callback failed (G)");
-    return N2V2R_ECOMM;
-  }
-  RC(launch_smallmat(s, 2, l, b.G, nullptr, b.W, b.lam, b.C, b.C2, b.flag));
+  // embeddings from the last Rayleigh-Ritz application: Z_t W Sigma^-1/2 ; left = Q W Sigma^1/2
+  RC(launch_smallmat(s, 2, l, b.H, nullptr, b.W, b.lam, b.C, b.C2, b.flag));
   for (int t = 0; t < T; ++t)
     RC(launch_apply_small(s, b.Z + t * nl, n, l, b.C, l, k, d_embed + (size_t)t * n * k, k, nullptr, nullptr, nullptr, nullptr, nullptr));
   if (d_left) RC(launch_apply_small(s, b.Q, n, l, b.C2, l, k, d_left, k, nullptr, nullptr, nullptr, nullptr, nullptr));
-  stats.kernel_launches += 2 * T + 1 + T + (d_left ? 1 : 0);
-  N2V2R_CUDA(cudaMemcpyAsync(lam.data(), b.lam, sizeof(double) * l, cudaMemcpyDeviceToHost, s));
+  stats.kernel_launches += 1 + T + (d_left ? 1 : 0);
   N2V2R_CUDA(cudaEventRecord(ev_all1, s));
   N2V2R_CUDA(cudaStreamSynchronize(s));
   for (int j = 0; j < k; ++j) h_sigma[j] = sqrt(std::max(lam[j], 0.0));
@@ -185,19 +267,27 @@ extern "C" int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2
     stats.stream_ms += ms;
     cudaEventDestroy(evs[e]); cudaEventDestroy(evs[e + 1]);
   }
+  for (size_t e = 0; e + 1 < mma_evs.size(); e += 2) {
+    N2V2R_CUDA(cudaEventElapsedTime(&ms, mma_evs[e], mma_evs[e + 1]));
+    stats.mma_ms += ms;
+    cudaEventDestroy(mma_evs[e]); cudaEventDestroy(mma_evs[e + 1]);
+  }
+  stats.mma_launches = (int)(mma_evs.size() / 2);
   N2V2R_CUDA(cudaEventElapsedTime(&ms, ev_all0, ev_all1));
   stats.total_ms = ms;
   cudaEventDestroy(ev_all0); cudaEventDestroy(ev_all1);
-  stats.iterations = it;
-  stats.converged = converged ? 1 : 0;
+  stats.outer_iterations = outer;
+  stats.locked = locked;
+  stats.converged = converged ? (stagnated && !(bound <= p->tol) ? 2 : 1) : 0;   // 2 = stopped at the fp32 residual floor
   stats.max_angle_bound = bound;
   for (int j = 0; j < l && j < 96; ++j) {
     stats.ritz[j] = lam[j];
-    stats.resid[j] = lam[j] > 0 ? sqrt(std::max(res[j], 0.0)) / lam[j] : 0.0;
+    stats.resid[j] = lam[0] > 0 ? res[j] / lam[0] : 0.0;     // residual norms relative to lam_1
   }
   if (st) *st = stats;
-  if (!converged && !stagnated) {
-    set_error("uase: reached max_iters=%d with subspace-angle bound %.3e > tol %.3e", p->max_iters, bound, p->tol);
+  if (!converged) {
+    set_error("uase: reached max_iters=%d operator applications with subspace-angle bound %.3e > tol %.3e (%d of %d Ritz pairs at the residual floor)",
+              p->max_iters, bound, p->tol, locked, k);
     return N2V2R_ENOTCONV;
   }
   return N2V2R_OK;

@@ -216,7 +216,7 @@ def preprocess_to_layer(x: torch.Tensor, threshold=None, top_percent_keep=100, b
 
 
 def uase(layers, k, l=64, tol=1e-5, max_iters=300, min_iters=2, seed=42, check_dims=None, algo=N.ALGO_TCGEN05,
-         k_chunk=0, allreduce=None, T_global=None, layer_offset=0, want_left=False):
+         k_chunk=0, allreduce=None, T_global=None, layer_offset=0, want_left=False, cheb_degree=0):
     """K3-K8: returns (embeddings (T_local, n, k) fp32 device, sigma (k,) float64, left | None, stats dict)."""
     lib = N.load()
     dev = _dev()
@@ -224,7 +224,7 @@ def uase(layers, k, l=64, tol=1e-5, max_iters=300, min_iters=2, seed=42, check_d
     n = layers[0].n
     dims = np.asarray(sorted(set(int(d) for d in (check_dims or [k]) if 1 <= int(d) <= k)), dtype=np.int32)
     p = N.UaseParams(n=n, T_local=T, T_global=T_global or T, layer_offset=layer_offset, k=k, l=l,
-                     max_iters=max_iters, min_iters=min_iters, cheb_degree=1, algo=algo, k_chunk=k_chunk,
+                     max_iters=max_iters, min_iters=min_iters, cheb_degree=cheb_degree, algo=algo, k_chunk=k_chunk,
                      n_check=len(dims), tol=tol, seed=seed,
                      h_check_dims=dims.ctypes.data_as(C.POINTER(C.c_int32)))
     ws_bytes = lib.n2v2r_uase_workspace_bytes(C.byref(p))
@@ -241,7 +241,8 @@ def uase(layers, k, l=64, tol=1e-5, max_iters=300, min_iters=2, seed=42, check_d
                         sigma.ctypes.data_as(C.POINTER(C.c_double)), C.byref(stats))
     N.check(rc, allow=(N.ENOTCONV,))
     info = dict(iterations=stats.iterations, layer_passes=stats.layer_passes, converged=bool(stats.converged),
-                kernel_launches=stats.kernel_launches, stream_ms=stats.stream_ms, total_ms=stats.total_ms,
+                kernel_launches=stats.kernel_launches, outer_iterations=stats.outer_iterations,
+                locked=stats.locked, stream_ms=stats.stream_ms, mma_ms=stats.mma_ms, mma_launches=stats.mma_launches, total_ms=stats.total_ms,
                 stream_bytes=stats.stream_bytes, angle_bound=stats.max_angle_bound,
                 resid=np.asarray(stats.resid[:l]), ritz=np.asarray(stats.ritz[:l]), status=rc, l=l)
     return emb, sigma, left, info
