@@ -1,0 +1,363 @@
+#!/usr/bin/env python
+"""Benchmark of the UASE embed-and-rank hot path (BASELINE.json metric) on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload c3|c2]
+
+A step = one pass of the hot path over one synthetic multi-layer SBM: UASE solve at k = 24
+(streaming tcgen05 products + CholeskyQR2 + Jacobi), distances for every swept d (4..24, euclidean +
+cosine), per-column rank and Borda.  `value` = wall time per step with the preprocessed layers
+resident in HBM (CUDA events, max over ranks); `e2e` = the same through the public N2V2R API with
+the transformed graphs in pinned HOST memory (H2D of the graphs, plane build, solve, rank, D2H of
+the tables inside the timed region).  Layers are sharded over the ranks (strong scaling: the
+workload is fixed); the only data-path collective is the all-reduce of Y (n x l) per operator
+application plus one all-gather of the embeddings.
+
+`--impl reference` times the reference's own CPU path (oracle/reference_port.py: scipy svds/ARPACK on
+CSC layers, scipy.spatial distances, pandas sort + joblib Borda -- SURVEY 8c) on a bounded sample.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np
+
+DIMS = list(range(4, 25, 2))
+METRICS = ["euclidean", "cosine"]
+WORKLOADS = {
+    # BASELINE.json configs[2]: the configuration the metric is quoted on (fits one B200: 80 GB of planes)
+    "c3": dict(n=50000, T=8, K=32, weighted=True, keep=10, binarize=False, strategy="one_vs_rest",
+               name="synthetic 8-layer weighted SBM n=50k, top_percent_keep=10, one_vs_rest, d=4..24, euclidean+cosine, Borda"),
+    # BASELINE.json configs[1]
+    "c2": dict(n=20000, T=2, K=32, weighted=False, keep=100, binarize=True, strategy="sequential",
+               name="synthetic 2-layer dense SBM n=20k, binarize, sequential, d=4..24, euclidean+cosine, Borda"),
+}
+CPU_SAMPLE_N = 3000
+GRAPH_SEED = 1
+SOLVER_SEED = 42
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
+    ap.add_argument("--n", type=int, default=0, help="override the node count (development only; named in config.workload)")
+    ap.add_argument("--block-width", type=int, default=64)
+    ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer end-to-end leg (development only)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (development only)")
+    return ap.parse_args()
+
+
+# ---- clocks ------------------------------------------------------------------------------------
+class ClockSampler:
+    FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.path = tempfile.mktemp(prefix="n2v2r_clocks_", suffix=".csv")
+        self.proc = None
+        self.gpu = gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except OSError:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        try:
+            for line in open(self.path):
+                f = [x.strip() for x in line.split(",")]
+                if len(f) < 9:
+                    continue
+                try:
+                    sm.append(float(f[1])); mx.append(float(f[2]))
+                except ValueError:
+                    continue
+                for nm, v in zip(names, f[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+            os.unlink(self.path)
+        except OSError:
+            pass
+        if sm:
+            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(mx)), reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+# ---- workload helpers --------------------------------------------------------------------------
+def workload_of(args):
+    w = dict(WORKLOADS[args.workload])
+    if args.n:
+        w["n"] = args.n
+        w["name"] += f" [development override n={args.n}]"
+    return w
+
+
+def block_probabilities(w):
+    from node2vec2rank_b200.synthetic import block_matrices
+    return block_matrices(w["K"], w["T"], seed=GRAPH_SEED)[0]
+
+
+# ---- CPU legs: the reference's own algorithm through the oracle port -----------------------------
+def cpu_sample_graphs(w, n):
+    """Transformed fp32 layers of the sample, made like the reference does (preprocessing_utils.py:116-141)."""
+    from node2vec2rank_b200.synthetic import sbm_layer_numpy
+    from oracle import reference_port as port
+    Bs = block_probabilities(w)
+    out = []
+    for t in range(w["T"]):
+        raw = sbm_layer_numpy(n, w["K"], Bs[t], GRAPH_SEED, t, w["weighted"])
+        out.append(port.network_transform(raw.astype(np.float64), top_percent_keep=w["keep"], binarize=w["binarize"]))
+    return out
+
+
+def cpu_step(graphs, w):
+    """model.py:98-201 on transformed graphs: csc_matrix + UASE(svds/ARPACK) + distances + sort + joblib Borda."""
+    from oracle import reference_port as port
+    tm = {}
+    np.random.seed(SOLVER_SEED)
+    port.fit_rank_borda(graphs, DIMS, METRICS, w["strategy"], faithful=True, timings=tm)
+    return tm
+
+
+def cpu_cores_used():
+    n = os.cpu_count() or 1
+    return max(1, n - 1)        # joblib n_jobs=-2 in Borda; ARPACK / csc matvec / scipy distances are single-threaded
+
+
+def scale_to_full(seconds, w, n_sample):
+    """Linear in matrix entries (T n^2): a LOWER bound for the reference, whose fit grows ~n^2.4."""
+    return seconds * (w["n"] / n_sample) ** 2
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    w = workload_of(args)
+    n_s = min(CPU_SAMPLE_N, w["n"])
+    graphs = cpu_sample_graphs(w, n_s)
+    for _ in range(args.warmup):
+        cpu_step(graphs, w)
+    t0 = time.perf_counter()
+    parts = [cpu_step(graphs, w) for _ in range(args.steps)]
+    dt = (time.perf_counter() - t0) / max(args.steps, 1)
+    full = scale_to_full(dt, w, n_s)
+    sample = (f"n={n_s} of {w['n']} nodes, all {w['T']} layers, same transform/sweep; measured {dt:.2f} s/step "
+              f"(fit {np.mean([p['fit'] for p in parts]):.2f}, distances {np.mean([p['distances'] for p in parts]):.2f}, "
+              f"borda {np.mean([p['borda'] for p in parts]):.2f}); value = measured x (n_full/n_sample)^2, linear in matrix "
+              f"entries -- a lower bound, the reference's fit grows ~n^2.4")
+    line = {
+        "impl": "reference", "metric": "UASE sweep+rank wall time", "value": full, "unit": "s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": full * 1e3, "higher_is_better": False, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": w["name"], "n": w["n"], "layers": w["T"], "communities": w["K"]},
+        "cpu_baseline": {"value": full, "unit": "s", "cores": cpu_cores_used(), "kind": "port", "sample": sample,
+                         "sample_seconds": dt},
+        "e2e": {"value": full, "unit": "s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ---- B200 arm ------------------------------------------------------------------------------------
+def run_b200_arm(args):
+    import torch
+    import torch.distributed as tdist
+    from node2vec2rank_b200 import _native as N
+    from node2vec2rank_b200 import device as D
+    from node2vec2rank_b200 import dist as ND
+    from node2vec2rank_b200.model import N2V2R
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    dev = N.require_gpu()
+    if world > 1:
+        tdist.init_process_group("nccl", device_id=dev)
+    w = workload_of(args)
+    n, T, K, l = w["n"], w["T"], w["K"], args.block_width
+    mine = ND.layer_partition(T, world, rank)
+    Bs = block_probabilities(w)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except (OSError, ValueError):
+        pass
+    hbm_peak, peak_src = (float(peaks["hbm_gbs"]), "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
+
+    def barrier():
+        if world > 1:
+            tdist.barrier()
+        torch.cuda.synchronize()
+
+    def reduce_max(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        tdist.all_reduce(t, op=tdist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- setup (untimed): K0 generate + K1 load pass per local layer -------------------------------
+    t_setup = time.perf_counter()
+    layers, host_graphs = [], []
+    for t in mine:
+        raw = D.sbm_generate(n, K, Bs[t], seed=GRAPH_SEED, layer=t, weighted=w["weighted"])
+        layer, f32 = D.preprocess_to_layer(raw, top_percent_keep=w["keep"], binarize=w["binarize"], want_f32=not args.no_e2e)
+        del raw
+        if f32 is not None:            # what the reference's DataLoader hands to N2V2R: float32 (n, n) on the HOST (pinned)
+            h = torch.empty((n, n), dtype=torch.float32, pin_memory=True)
+            h.copy_(f32)
+            host_graphs.append(h.numpy())
+            del f32
+        layers.append(layer)
+    torch.cuda.synchronize()
+    n_planes = layers[0].n_planes if layers else 0
+    setup_s = time.perf_counter() - t_setup
+    names, cdims, cmets = D.column_specs(DIMS, METRICS)
+    strategy = N.STRATEGIES[w["strategy"]]
+
+    def step():
+        emb, sigma, _, info = D.uase(layers, max(DIMS), l=l, tol=1e-5, max_iters=400, seed=SOLVER_SEED, check_dims=DIMS,
+                                     T_global=T, layer_offset=mine.start if len(mine) else 0)
+        if world > 1:
+            emb = ND.gather_layers(emb, T)
+        scores = D.distances(emb, cdims, cmets, strategy)
+        bordas = [D.rank_borda(scores[c])[0] for c in range(scores.shape[0])]
+        launches = info["kernel_launches"] + 1 + len(bordas)
+        return info, scores, bordas, launches
+
+    for _ in range(args.warmup):
+        step()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    infos, launches = [], 0
+    for _ in range(args.steps):
+        info, scores, bordas, nl = step()
+        infos.append(info)
+        launches += nl
+    e1.record()
+    barrier()
+    ms_step = reduce_max(e0.elapsed_time(e1) / max(args.steps, 1))
+    clocks = sampler.stop() if rank == 0 else None
+
+    # ---- roofline of the dominant kernel (tcgen05 streaming product), measured live in the timed steps ----
+    mma_ms = sum(i["mma_ms"] for i in infos)
+    mma_n = sum(i["mma_launches"] for i in infos)
+    alg_bytes = float(n) * n * 2.0 * n_planes + 4.0 * l * 2.0 * n          # matrix once + skinny in + skinny out
+    achieved = alg_bytes / (mma_ms / max(mma_n, 1) * 1e-3) / 1e9 if mma_n else 0.0
+    stream_ms = sum(i["stream_ms"] for i in infos)
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
+                "traffic": None, "kernel": "stream_mma_kernel", "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": alg_bytes, "launches_per_step": mma_n / max(args.steps, 1),
+                "avg_launch_ms": mma_ms / max(mma_n, 1), "share_of_step": mma_ms / max(ms_step * args.steps, 1e-9),
+                "streaming_products_share_of_step": stream_ms / max(ms_step * args.steps, 1e-9)}
+    traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(traffic_file):
+        try:
+            roofline["traffic"] = json.load(open(traffic_file)).get(f"{args.workload}_bytes_per_launch")
+        except ValueError:
+            pass
+
+    # ---- e2e: the public API on host buffers ------------------------------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        del layers, scores, bordas
+        torch.cuda.empty_cache()
+        cfg = dict(embed_dimensions=DIMS, distance_metrics=METRICS, comp_strategy=w["strategy"], seed=SOLVER_SEED,
+                   save_dir=None, verbose=-1, block_width=l, layer_sharded=world > 1)
+        node_names = np.arange(n)
+
+        def e2e_step():
+            m = N2V2R(graphs=host_graphs, nodes=node_names, config=cfg)
+            ranks = m.fit_transform_rank()              # H2D of the graphs + plane build + solve + distances + D2H of the tables
+            agg = m.aggregate_transform()               # rank + Borda + D2H
+            d2h = m.node_embeddings.shape[0] * n * max(DIMS) * 4 + sum(v.shape[0] * v.shape[1] * 8 for v in ranks.values()) \
+                + sum(v.shape[0] * 8 for v in agg.values())
+            return d2h
+
+        for _ in range(args.warmup):
+            e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        d2h = 0
+        for _ in range(args.steps):
+            d2h = e2e_step()
+        barrier()
+        e2e_s = reduce_max((time.perf_counter() - t0) / max(args.steps, 1))
+        e2e = {"value": e2e_s, "unit": "s", "h2d_bytes_per_step": int(T) * n * n * 4, "d2h_bytes_per_step": int(d2h),
+               "api": "N2V2R(graphs=float32 host arrays).fit_transform_rank() + aggregate_transform()"}
+
+    if rank != 0:
+        if world > 1:
+            tdist.destroy_process_group()
+        return 0
+    # ---- cpu_baseline (rank 0, N = 1 only) -------------------------------------------------------------
+    cpu = None
+    if world == 1 and not args.no_cpu:
+        n_s = min(CPU_SAMPLE_N, n)
+        g = cpu_sample_graphs(w, n_s)
+        tm = cpu_step(g, w)
+        cpu = {"value": scale_to_full(tm["total"], w, n_s), "unit": "s", "cores": cpu_cores_used(), "kind": "port",
+               "sample": f"n={n_s} of {n} nodes, all {T} layers, one step; measured {tm['total']:.2f} s (fit {tm['fit']:.2f}, distances "
+                         f"{tm['distances']:.2f}, borda {tm['borda']:.2f}); value = measured x (n_full/n_sample)^2 (lower bound)",
+               "sample_seconds": tm["total"]}
+    last = infos[-1]
+    line = {
+        "metric": "UASE sweep+rank wall time", "value": ms_step / 1e3, "unit": "s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": False, "scaling": "strong", "vs_baseline": None,
+        "dtype": "bf16 planes x3-split bf16 operand, fp32 accumulate (tcgen05), fp64 small dense",
+        "data": "synthetic",
+        "config": {"workload": w["name"], "n": n, "layers": T, "communities": K, "block_width": l, "planes_per_layer": n_planes,
+                   "layers_per_gpu": len(mine), "l2_policy": "inputs larger than L2 (each layer pass streams >= 5 GB)",
+                   "operator_applications": last["iterations"], "layer_passes": last["layer_passes"],
+                   "outer_iterations": last["outer_iterations"], "converged": last["converged"],
+                   "angle_bound": last["angle_bound"], "setup_s": setup_s},
+        "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        tdist.destroy_process_group()
+    return 0
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return run_reference_arm(args)
+    return run_b200_arm(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -216,7 +216,7 @@ def preprocess_to_layer(x: torch.Tensor, threshold=None, top_percent_keep=100, b
 
 
 def uase(layers, k, l=64, tol=1e-5, max_iters=300, min_iters=2, seed=42, check_dims=None, algo=N.ALGO_TCGEN05,
-         k_chunk=0, allreduce=None, T_global=None, layer_offset=0, want_left=False, cheb_degree=0):
+         k_chunk=0, allreduce=None, T_global=None, layer_offset=0, want_left=False, cheb_degree=0, group=None):
     """K3-K8: returns (embeddings (T_local, n, k) fp32 device, sigma (k,) float64, left | None, stats dict)."""
     lib = N.load()
     dev = _dev()
@@ -236,11 +236,21 @@ def uase(layers, k, l=64, tol=1e-5, max_iters=300, min_iters=2, seed=42, check_d
     sigma = np.zeros(k, dtype=np.float64)
     stats = N.UaseStats()
     arr = (N.Layer * T)(*[L.c_struct() for L in layers])
-    cb = N.ALLREDUCE_FN(allreduce) if allreduce is not None else C.cast(None, N.ALLREDUCE_FN)
+    state = None
+    if allreduce is not None:
+        cb = N.ALLREDUCE_FN(allreduce)
+    elif (T_global or T) > T:                    # layer-sharded: all-reduce Y over the ranks (dist.py)
+        from . import dist
+        cb, state = dist.make_allreduce_callback(ws, group)
+    else:
+        cb = C.cast(None, N.ALLREDUCE_FN)
     rc = lib.n2v2r_uase(N.stream_ptr(), C.byref(p), arr, N.ptr(ws), ws_bytes, cb, None, N.ptr(emb), N.ptr(left),
                         sigma.ctypes.data_as(C.POINTER(C.c_double)), C.byref(stats))
+    if state is not None and state["error"] is not None:
+        raise state["error"]
     N.check(rc, allow=(N.ENOTCONV,))
-    info = dict(iterations=stats.iterations, layer_passes=stats.layer_passes, converged=bool(stats.converged),
+    info = dict(allreduce_calls=0 if state is None else state["calls"], allreduce_bytes=0 if state is None else state["bytes"],
+                iterations=stats.iterations, layer_passes=stats.layer_passes, converged=bool(stats.converged),
                 kernel_launches=stats.kernel_launches, outer_iterations=stats.outer_iterations,
                 locked=stats.locked, stream_ms=stats.stream_ms, mma_ms=stats.mma_ms, mma_launches=stats.mma_launches, total_ms=stats.total_ms,
                 stream_bytes=stats.stream_bytes, angle_bound=stats.max_angle_bound,

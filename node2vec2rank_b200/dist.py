@@ -1,0 +1,82 @@
+"""Layer sharding across GPUs: one process per GPU, torch.distributed for the plumbing.
+
+The unfolded operator splits by layer: [A_1|...|A_T] X = sum_t A_t X_t and (A^T Q)_t = A_t^T Q.
+Rank r owns a contiguous block of layers; Z_t = A_t^T Q and the per-layer embeddings stay local,
+and the only exchange per operator application is an all-reduce of Y = sum_t A_t Z_t (n x l fp32)
+-- the solver calls back into `make_allreduce_callback` for it.  Every rank then runs the same
+(deterministic) small dense steps on the same reduced data, so Q stays replicated bit for bit.
+The per-layer embeddings are all-gathered once at the end for the ranking kernels.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _native as N
+
+
+def is_distributed():
+    return torch.distributed.is_available() and torch.distributed.is_initialized() and torch.distributed.get_world_size() > 1
+
+
+def layer_partition(T, world_size, rank):
+    """Contiguous block of layers owned by `rank`: the first T % world ranks get one extra layer."""
+    if world_size < 1 or not (0 <= rank < world_size):
+        raise ValueError("bad world_size / rank")
+    base, extra = divmod(T, world_size)
+    start = rank * base + min(rank, extra)
+    return range(start, start + base + (1 if rank < extra else 0))
+
+
+_TORCH_DTYPE = {N.F32: torch.float32, N.F64: torch.float64}
+
+
+def make_allreduce_callback(workspace: torch.Tensor, group=None):
+    """ctypes callback (n2v2r_allreduce_fn) summing a sub-range of `workspace` over all ranks, in place.
+
+    The solver hands back raw pointers into the workspace it was given; the callback turns
+    (pointer, count, dtype) into a view of that tensor and calls torch.distributed.all_reduce on it
+    (NCCL on GPU tensors, ordered after the kernels already queued on the current stream; gloo on
+    CPU tensors in the tests).  Returns (callback, state) -- keep both alive during the solve."""
+    base = workspace.data_ptr()
+    nbytes = workspace.numel() * workspace.element_size()
+    flat = workspace.view(torch.uint8).reshape(-1)
+    state = {"calls": 0, "bytes": 0, "error": None}
+
+    def _cb(_user, ptr, count, dtype, _stream):
+        try:
+            tdt = _TORCH_DTYPE[dtype]
+            size = torch.empty((), dtype=tdt).element_size()
+            off = int(ptr) - base
+            if off < 0 or off + count * size > nbytes or off % size:
+                raise ValueError("all-reduce range outside the workspace")
+            view = flat[off:off + count * size].view(tdt)
+            torch.distributed.all_reduce(view, op=torch.distributed.ReduceOp.SUM, group=group)
+            state["calls"] += 1
+            state["bytes"] += count * size
+            return 0
+        except Exception as exc:            # never let an exception cross the C boundary
+            state["error"] = exc
+            return 1
+
+    return N.ALLREDUCE_FN(_cb), state
+
+
+def gather_layers(local: torch.Tensor, T, group=None):
+    """All-gather the per-layer blocks (T_local, n, k) of every rank into (T, n, k), in layer order."""
+    world = torch.distributed.get_world_size(group)
+    rank = torch.distributed.get_rank(group)
+    counts = [len(layer_partition(T, world, r)) for r in range(world)]
+    if local.shape[0] != counts[rank]:
+        raise ValueError(f"rank {rank} holds {local.shape[0]} layers, partition says {counts[rank]}")
+    width = max(counts)
+    n, k = local.shape[1], local.shape[2]
+    pad = torch.zeros((width, n, k), dtype=local.dtype, device=local.device)
+    pad[:counts[rank]] = local
+    out = [torch.empty_like(pad) for _ in range(world)]
+    torch.distributed.all_gather(out, pad, group=group)
+    return torch.cat([o[:c] for o, c in zip(out, counts)], dim=0)
+
+
+__all__ = ["is_distributed", "layer_partition", "make_allreduce_callback", "gather_layers"]

@@ -10,6 +10,9 @@ Additive, optional config keys (defaults keep reference behaviour):
   block_width (int, default: max dim + >=24 guard vectors rounded up to 16): solver block l
   solver_tol (float, default 1e-5), solver_max_iters (int, default 400)
   storage_planes (int | None): bf16 planes per weighted layer (None = exact)
+  layer_sharded (bool, default False): under torch.distributed (one process per GPU) `graphs` holds only
+      this rank's contiguous block of layers (dist.layer_partition); Y is all-reduced per operator
+      application, embeddings are all-gathered, every rank returns the full tables
 """
 from __future__ import annotations
 
@@ -25,6 +28,7 @@ import torch
 
 from . import _native as N
 from . import device as D
+from . import dist
 from .model_utils import signed_transform_single
 
 
@@ -79,6 +83,14 @@ class N2V2R:
             self._layers = layers
         return self._layers
 
+    def _global_layers(self, layers):
+        """(total number of layers over all ranks, index of this rank's first layer)."""
+        counts = torch.tensor([len(layers)], device=layers[0].planes.device)
+        allc = [torch.zeros_like(counts) for _ in range(torch.distributed.get_world_size())]
+        torch.distributed.all_gather(allc, counts)
+        vals = [int(c.item()) for c in allc]
+        return sum(vals), sum(vals[:torch.distributed.get_rank()])
+
     def _solver_seed(self):
         seed = self.config.get("seed")
         if seed:
@@ -93,9 +105,17 @@ class N2V2R:
         if k >= n:                                      # scipy svds: "k must satisfy 0 < k < min(A.shape)"
             raise ValueError(f"`k` must be an integer satisfying `0 < k < min(A.shape)` (k={k}, n={n}).")
         l = int(self.config.get("block_width") or D.default_block_width(k, n))
+        T_global, offset = len(layers), 0
+        sharded = bool(self.config.get("layer_sharded")) and dist.is_distributed()
+        if sharded:
+            T_global, offset = self._global_layers(layers)
         emb, sigma, _, info = D.uase(layers, k, l=l, tol=float(self.config.get("solver_tol", 1e-5)),
                                      max_iters=int(self.config.get("solver_max_iters", 400)),
-                                     seed=self._solver_seed(), check_dims=self.embed_dimensions)
+                                     seed=self._solver_seed(), check_dims=self.embed_dimensions,
+                                     T_global=T_global, layer_offset=offset)
+        if sharded:
+            emb = dist.gather_layers(emb, T_global)
+        self.num_graphs = T_global
         self._emb_dev = emb
         self.singular_values = sigma
         self.solver_info = info
@@ -220,9 +240,12 @@ class N2V2R:
         for L in layers:
             if L.colsum is None:
                 L.colsum = D.column_sums(L)
-            sums.append(L.colsum.cpu().numpy().astype(np.float32))      # np.sum of an fp32 matrix is fp32
+            sums.append(L.colsum)
+        if bool(self.config.get("layer_sharded")) and dist.is_distributed():
+            sums = list(dist.gather_layers(torch.stack(sums)[:, :, None], self._global_layers(layers)[0])[:, :, 0])
+        sums = [c.cpu().numpy().astype(np.float32) for c in sums]           # np.sum of an fp32 matrix is fp32
         pairwise = {}
-        for i in range(1, len(layers)):
+        for i in range(1, len(sums)):
             DeDi = sums[i - 1] - sums[i]
             ranking = pd.DataFrame.from_dict({"DeDi": DeDi, "absDeDi": np.abs(DeDi)})
             ranking.index = self.node_names
