@@ -203,11 +203,12 @@ int n2v2r_distances(void* stream, const void* d_embed, int dtype, int T, int64_t
  * order-preserving 64-bit pattern; ties stable by node position; NaN last) and Borda
  * points sum_c (n - position_c).  Replaces aggregate_transform (model.py:167-185) +
  * borda_aggregate_parallel/_get_ranking (model_utils.py:22-36).
- * d_scores: (n_cols x n) doubles; d_positions: (n_cols x n) int32 or NULL;
- * d_borda: n int64.
+ * d_scores: (n_cols x n) doubles, n_cols = n_groups * columns per comparison; d_positions:
+ * (n_cols x n) int32 or NULL; d_borda: (n_groups x n) int64, one Borda table per group of
+ * consecutive columns (all comparisons of a run are ranked by one launch).
  * ---------------------------------------------------------------------------------- */
 size_t n2v2r_rank_workspace_bytes(int64_t n, int n_cols);
-int n2v2r_rank_borda(void* stream, const double* d_scores, int64_t n, int n_cols,
+int n2v2r_rank_borda(void* stream, const double* d_scores, int64_t n, int n_cols, int n_groups,
                      int32_t* d_positions, int64_t* d_borda, void* d_ws, size_t ws_bytes);
 
 #ifdef __cplusplus

@@ -7,7 +7,8 @@
 namespace n2v2r {
 
 // ---- X^T Y partials: each CTA reduces a slab of rows into an l x l fp64 block ------------
-// 256 threads; thread owns entries e = tid, tid+256, ... of the l*l output.
+// 256 threads as 16 x 16; thread (ag, bg) owns out[ag + 16 i][bg + 16 j], i, j < 5 (l <= 80):
+// 25 fp64 accumulators in registers, per row 5 + 5 shared loads for 25 DFMA.
 __global__ void __launch_bounds__(256) xty_kernel(const float* __restrict__ X, const float* __restrict__ Y, int64_t n, int l,
                                                   int rows_per_cta, double* __restrict__ partials) {
   extern __shared__ float sm[];             // 2 * 32 * l
@@ -15,10 +16,12 @@ __global__ void __launch_bounds__(256) xty_kernel(const float* __restrict__ X, c
   float* sy = sm + 32 * l;
   const int64_t r0 = (int64_t)blockIdx.x * rows_per_cta;
   const int64_t r1 = (r0 + rows_per_cta < n) ? r0 + rows_per_cta : n;
-  const int ll = l * l;
-  double acc[25];                           // ceil(80*80/256) = 25
+  const int ag = threadIdx.x & 15, bg = threadIdx.x >> 4;
+  double acc[5][5];
 #pragma unroll
-  for (int q = 0; q < 25; ++q) acc[q] = 0.0;
+  for (int i = 0; i < 5; ++i)
+#pragma unroll
+    for (int j = 0; j < 5; ++j) acc[i][j] = 0.0;
   for (int64_t rb = r0; rb < r1; rb += 32) {
     const int rows = (int)((r1 - rb < 32) ? (r1 - rb) : 32);
     for (int t = threadIdx.x; t < 32 * l; t += 256) {
@@ -27,24 +30,28 @@ __global__ void __launch_bounds__(256) xty_kernel(const float* __restrict__ X, c
       sy[t] = r < rows ? Y[(rb + r) * l + (t - r * l)] : 0.f;
     }
     __syncthreads();
+#pragma unroll 4
+    for (int r = 0; r < 32; ++r) {
+      double xv[5], yv[5];
 #pragma unroll
-    for (int q = 0; q < 25; ++q) {
-      const int e = threadIdx.x + q * 256;
-      if (e < ll) {
-        const int a = e / l, b = e - a * l;
-        double s = 0.0;
-#pragma unroll 8
-        for (int r = 0; r < 32; ++r) s += (double)sx[r * l + a] * (double)sy[r * l + b];
-        acc[q] += s;
+      for (int i = 0; i < 5; ++i) {
+        xv[i] = (ag + 16 * i < l) ? (double)sx[r * l + ag + 16 * i] : 0.0;
+        yv[i] = (bg + 16 * i < l) ? (double)sy[r * l + bg + 16 * i] : 0.0;
       }
+#pragma unroll
+      for (int i = 0; i < 5; ++i)
+#pragma unroll
+        for (int j = 0; j < 5; ++j) acc[i][j] = fma(xv[i], yv[j], acc[i][j]);
     }
     __syncthreads();
   }
 #pragma unroll
-  for (int q = 0; q < 25; ++q) {
-    const int e = threadIdx.x + q * 256;
-    if (e < ll) partials[(size_t)blockIdx.x * ll + e] = acc[q];
-  }
+  for (int i = 0; i < 5; ++i)
+#pragma unroll
+    for (int j = 0; j < 5; ++j) {
+      const int a_ = ag + 16 * i, b_ = bg + 16 * j;
+      if (a_ < l && b_ < l) partials[(size_t)blockIdx.x * l * l + a_ * l + b_] = acc[i][j];
+    }
 }
 
 // fixed-order sum of the per-CTA partials (deterministic)
@@ -273,69 +280,74 @@ __global__ void __launch_bounds__(512) smallmat_kernel(int mode, int l, const do
   }
 }
 
-// ---- Out[n][lo] = X[n][l] * C[l][lo]  (+ optional residual column norms) --------------------
-// 128 threads, 32 rows per tile; thread (r = tid/4, g = tid%4) computes columns g, g+4, ...
-// With resid != nullptr also accumulates ||Y W - Q W Lam||^2 per column (partials per CTA).
-__global__ void __launch_bounds__(128) apply_small_kernel(const float* __restrict__ X, int64_t n, int l, const double* __restrict__ C,
-                                                          int ldc, int lo, float* __restrict__ Out, int64_t ld_out,
-                                                          const float* __restrict__ Qm, const double* __restrict__ W,
-                                                          const double* __restrict__ lam, double* __restrict__ resid_partials,
-                                                          int tiles_per_cta) {
+// ---- Out[n][lo] = X[n][l] * C[l][lo], fp64 accumulate -----------------------------------------
+// 256 threads as 16 (row groups of 4) x 16 (column groups: j = cg + 16 q, q < 5); tile = 64 rows.
+__global__ void __launch_bounds__(256) apply_small_kernel(const float* __restrict__ X, int64_t n, int l, const double* __restrict__ C,
+                                                          int ldc, int lo, float* __restrict__ Out, int64_t ld_out) {
   extern __shared__ double sd[];
-  double* sC = sd;                         // l * lo
-  double* sW = sC + l * lo;                // l * l (only with resid)
-  float* sx = (float*)(sW + (resid_partials ? l * l : 0));   // 32 * l
-  float* sq = sx + 32 * l;                 // 32 * l (only with resid)
-  for (int e = threadIdx.x; e < l * lo; e += 128) sC[e] = C[(e / lo) * ldc + (e % lo)];
-  if (resid_partials) for (int e = threadIdx.x; e < l * l; e += 128) sW[e] = W[e];
-  const int r = threadIdx.x >> 2, g = threadIdx.x & 3;
-  double racc[20];
+  double* sC = sd;                               // l * lo
+  float* sx = (float*)(sC + (size_t)l * lo);     // 64 * (l + 1)
+  const int ls = l + 1;
+  for (int e = threadIdx.x; e < l * lo; e += 256) sC[e] = C[(e / lo) * ldc + (e % lo)];
+  const int cg = threadIdx.x & 15, rg = threadIdx.x >> 4;
+  for (int64_t rb = (int64_t)blockIdx.x * 64; rb < n; rb += (int64_t)gridDim.x * 64) {
+    __syncthreads();
+    for (int e = threadIdx.x; e < 64 * l; e += 256) {
+      const int r = e / l, c = e - r * l;
+      sx[r * ls + c] = (rb + r < n) ? X[(rb + r) * l + c] : 0.f;
+    }
+    __syncthreads();
+    double acc[4][5];
 #pragma unroll
-  for (int q = 0; q < 20; ++q) racc[q] = 0.0;
-  for (int t = 0; t < tiles_per_cta; ++t) {
-    const int64_t rb = ((int64_t)blockIdx.x * tiles_per_cta + t) * 32;
-    if (rb >= n) break;
-    __syncthreads();
-    for (int e = threadIdx.x; e < 32 * l; e += 128) {
-      const int rr = e / l;
-      const bool ok = rb + rr < n;
-      sx[e] = ok ? X[(rb + rr) * l + (e - rr * l)] : 0.f;
-      if (resid_partials) sq[e] = ok ? Qm[(rb + rr) * l + (e - rr * l)] : 0.f;
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int q = 0; q < 5; ++q) acc[i][q] = 0.0;
+    for (int k = 0; k < l; ++k) {
+      double xv[4], cv[5];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) xv[i] = (double)sx[(rg * 4 + i) * ls + k];
+#pragma unroll
+      for (int q = 0; q < 5; ++q) cv[q] = (cg + 16 * q < lo) ? sC[k * lo + cg + 16 * q] : 0.0;
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int q = 0; q < 5; ++q) acc[i][q] = fma(xv[i], cv[q], acc[i][q]);
     }
-    __syncthreads();
-    const bool ok = rb + r < n;
-    for (int j = g, q = 0; j < lo; j += 4, ++q) {
-      double s = 0.0;
-      for (int k = 0; k < l; ++k) s += (double)sx[r * l + k] * sC[k * lo + j];
-      if (ok) Out[(rb + r) * ld_out + j] = (float)s;
-    }
-    if (resid_partials) {
-      for (int j = g, q = 0; j < l; j += 4, ++q) {
-        double yw = 0.0, qw = 0.0;
-        for (int k = 0; k < l; ++k) { yw += (double)sx[r * l + k] * sW[k * l + j]; qw += (double)sq[r * l + k] * sW[k * l + j]; }
-        const double d = yw - qw * lam[j];
-        racc[q] += d * d;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int64_t row = rb + rg * 4 + i;
+      if (row < n) {
+#pragma unroll
+        for (int q = 0; q < 5; ++q)
+          if (cg + 16 * q < lo) Out[row * ld_out + cg + 16 * q] = (float)acc[i][q];
       }
     }
   }
-  if (resid_partials) {
-    // reduce over the 32 rows of the CTA: lanes with the same g are tid = 4*r + g
-    __syncthreads();
-    double* red = sd;                      // reuse sC region: 128 * 20 doubles <= l*lo? not guaranteed -> use sW (l*l >= 256)
-    red = sW;
-    for (int q = 0; q < 20; ++q) {
-      const int j = g + 4 * q;
-      if (j >= l) break;
-      double v = racc[q];
-      // rows r and r^1.. : reduce across lanes differing in bits 2..4 of lane id, then across 4 warps via smem
-      v += __shfl_xor_sync(0xffffffffu, v, 4);
-      v += __shfl_xor_sync(0xffffffffu, v, 8);
-      v += __shfl_xor_sync(0xffffffffu, v, 16);
-      if ((threadIdx.x & 31) < 4) red[(threadIdx.x >> 5) * l + j] = v;
+}
+
+// ---- residual column norms^2 of Yw - Qw diag(lam): per-CTA partials, summed in fixed order -----
+__global__ void __launch_bounds__(256) resid_kernel(const float* __restrict__ Yw, const float* __restrict__ Qw, int64_t n, int l,
+                                                    const double* __restrict__ lam, int rows_per_cta, double* __restrict__ partials) {
+  __shared__ double red[256];
+  const int64_t r0 = (int64_t)blockIdx.x * rows_per_cta;
+  const int64_t r1 = (r0 + rows_per_cta < n) ? r0 + rows_per_cta : n;
+  // thread -> column j = tid % l for rows tid / l, tid / l + 256 / l, ... (l divides into 256 unevenly: use a guard)
+  const int per = 256 / l;                       // row lanes per pass (>= 3 for l <= 80)
+  const int j = threadIdx.x % l, lane_r = threadIdx.x / l;
+  double acc = 0.0;
+  if (lane_r < per) {
+    const double lj = lam[j];
+    for (int64_t r = r0 + lane_r; r < r1; r += per) {
+      const double d = (double)Yw[r * l + j] - lj * (double)Qw[r * l + j];
+      acc = fma(d, d, acc);
     }
-    __syncthreads();
-    for (int j = threadIdx.x; j < l; j += 128)
-      resid_partials[(size_t)blockIdx.x * l + j] = red[j] + red[l + j] + red[2 * l + j] + red[3 * l + j];
+  }
+  red[threadIdx.x] = (lane_r < per) ? acc : 0.0;
+  __syncthreads();
+  if (threadIdx.x < l) {
+    double sacc = 0.0;
+    for (int q = 0; q < per; ++q) sacc += red[q * l + threadIdx.x];
+    partials[(size_t)blockIdx.x * l + threadIdx.x] = sacc;
   }
 }
 
@@ -438,23 +450,33 @@ int launch_smallmat(cudaStream_t s, int mode, int l, const double* H, const doub
   return N2V2R_OK;
 }
 
-int launch_apply_small(cudaStream_t s, const float* X, int64_t n, int l, const double* C, int ldc, int lo, float* Out, int64_t ld_out,
-                       const float* Qm, const double* W, const double* lam, double* resid_partials, int* n_parts) {
+int launch_apply_small(cudaStream_t s, const float* X, int64_t n, int l, const double* C, int ldc, int lo, float* Out, int64_t ld_out) {
   static bool done = false;
-  const size_t max_smem = sizeof(double) * (80 * 80 * 2) + sizeof(float) * 64 * 80;
+  const size_t max_smem = sizeof(double) * kMaxL * kMaxL + sizeof(float) * 64 * (kMaxL + 1);
   if (!done) {
     N2V2R_CUDA(cudaFuncSetAttribute(apply_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)max_smem));
     done = true;
   }
-  const int64_t tiles = (n + 31) / 32;
-  int grid = (int)(tiles < (int64_t)sm_count() * 4 ? tiles : (int64_t)sm_count() * 4);
-  const int tiles_per_cta = (int)((tiles + grid - 1) / grid);
-  grid = (int)((tiles + tiles_per_cta - 1) / tiles_per_cta);
-  const size_t smem = sizeof(double) * ((size_t)l * lo + (resid_partials ? (size_t)l * l : 0)) +
-                      sizeof(float) * 32 * l * (resid_partials ? 2 : 1);
-  apply_small_kernel<<<grid, 128, smem, s>>>(X, n, l, C, ldc, lo, Out, ld_out, Qm, W, lam, resid_partials, tiles_per_cta);
+  const int64_t tiles = (n + 63) / 64;
+  const int grid = (int)(tiles < (int64_t)sm_count() * 4 ? tiles : (int64_t)sm_count() * 4);
+  const size_t smem = sizeof(double) * (size_t)l * lo + sizeof(float) * 64 * (l + 1);
+  apply_small_kernel<<<grid, 256, smem, s>>>(X, n, l, C, ldc, lo, Out, ld_out);
   N2V2R_CHECK_LAUNCH();
-  if (n_parts) *n_parts = grid;
+  return N2V2R_OK;
+}
+
+// out[j] = || Yw[:, j] - lam[j] Qw[:, j] ||^2
+int launch_resid(cudaStream_t s, const float* Yw, const float* Qw, int64_t n, int l, const double* lam, double* partials,
+                 int max_parts, double* out) {
+  int parts = (int)((n + 255) / 256);
+  if (parts > max_parts) parts = max_parts;
+  if (parts < 1) parts = 1;
+  const int rows_per_cta = (int)((n + parts - 1) / parts);
+  parts = (int)((n + rows_per_cta - 1) / rows_per_cta);
+  resid_kernel<<<parts, 256, 0, s>>>(Yw, Qw, n, l, lam, rows_per_cta, partials);
+  N2V2R_CHECK_LAUNCH();
+  sum_partials_kernel<<<(l + 255) / 256, 256, 0, s>>>(partials, parts, l, out, 0);
+  N2V2R_CHECK_LAUNCH();
   return N2V2R_OK;
 }
 

@@ -15,9 +15,11 @@ int launch_xty(cudaStream_t s, const float* X, const float* Y, int64_t n, int l,
 // mode 0 RR, 1 CHOL, 2 FINAL -- see k5_orth.cu
 int launch_smallmat(cudaStream_t s, int mode, int l, const double* H, const double* S, double* W, double* lam, double* C,
                     double* C2, int* flag);
-// Out[n][lo] = X[n][l] C[l][lo]; optional residual partials ||Y W - Q W Lam||^2 (X plays Y)
-int launch_apply_small(cudaStream_t s, const float* X, int64_t n, int l, const double* C, int ldc, int lo, float* Out, int64_t ld_out,
-                       const float* Qm, const double* W, const double* lam, double* resid_partials, int* n_parts);
+// Out[n][lo] = X[n][l] C[l][lo]  (fp64 accumulate)
+int launch_apply_small(cudaStream_t s, const float* X, int64_t n, int l, const double* C, int ldc, int lo, float* Out, int64_t ld_out);
+// out[j] = ||Yw[:, j] - lam[j] Qw[:, j]||^2 ; partials: max_parts * l doubles
+int launch_resid(cudaStream_t s, const float* Yw, const float* Qw, int64_t n, int l, const double* lam, double* partials,
+                 int max_parts, double* out);
 // X -= U[:, :p] G[:p, :]  (deflation against the p locked Ritz vectors)
 int launch_sub_proj(cudaStream_t s, float* X, const float* U, int64_t n, int l, int p, const double* G);
 int launch_sum_partials(cudaStream_t s, const double* partials, int n_parts, int count, double* out);

@@ -70,7 +70,7 @@ __device__ __forceinline__ uint64_t rank_key(double s) {
 }
 
 // One CTA (1024 threads) sorts one column: LSD radix, 8-bit digits, stable.
-__global__ void __launch_bounds__(1024) rank_sort_kernel(const double* __restrict__ scores, int64_t n_, int n_cols,
+__global__ void __launch_bounds__(1024) rank_sort_kernel(const double* __restrict__ scores, int64_t n_, int n_cols, int cols_per_group,
                                                          uint64_t* __restrict__ keybuf, uint32_t* __restrict__ idxbuf,
                                                          int32_t* __restrict__ positions,
                                                          unsigned long long* __restrict__ borda) {
@@ -141,7 +141,7 @@ __global__ void __launch_bounds__(1024) rank_sort_kernel(const double* __restric
     for (int r = tid; r < n; r += 1024) {
       const uint32_t id = sorted[r];
       if (positions) positions[(size_t)col * n + id] = r;
-      atomicAdd(&borda[id], (unsigned long long)(n - r));      // model_utils.py:25: num_candidates - position
+      atomicAdd(&borda[(size_t)(col / cols_per_group) * n + id], (unsigned long long)(n - r));   // model_utils.py:25: num_candidates - position
     }
     __syncthreads();
   }
@@ -189,18 +189,19 @@ extern "C" size_t n2v2r_rank_workspace_bytes(int64_t n, int n_cols) {
   return align_up((size_t)n_cols * 2 * n * sizeof(uint64_t)) + align_up((size_t)n_cols * 2 * n * sizeof(uint32_t));
 }
 
-extern "C" int n2v2r_rank_borda(void* stream, const double* d_scores, int64_t n, int n_cols,
+extern "C" int n2v2r_rank_borda(void* stream, const double* d_scores, int64_t n, int n_cols, int n_groups,
                                 int32_t* d_positions, int64_t* d_borda, void* d_ws, size_t ws_bytes) {
   N2V2R_REQUIRE(d_scores && d_borda && d_ws, "rank_borda: null pointer");
-  N2V2R_REQUIRE(n > 0 && n < (1ll << 31) && n_cols >= 1, "rank_borda: bad shape");
+  N2V2R_REQUIRE(n > 0 && n < (1ll << 31) && n_cols >= 1 && n_groups >= 1 && n_cols % n_groups == 0,
+                "rank_borda: bad shape (n_cols must be a multiple of n_groups)");
   if (ws_bytes < n2v2r_rank_workspace_bytes(n, n_cols)) { set_error("rank_borda: workspace too small"); return N2V2R_ENOMEM; }
   cudaStream_t s = (cudaStream_t)stream;
   Arena a(d_ws, ws_bytes);
   uint64_t* keys = a.take<uint64_t>((size_t)n_cols * 2 * n);
   uint32_t* idx = a.take<uint32_t>((size_t)n_cols * 2 * n);
-  N2V2R_CUDA(cudaMemsetAsync(d_borda, 0, sizeof(int64_t) * n, s));
+  N2V2R_CUDA(cudaMemsetAsync(d_borda, 0, sizeof(int64_t) * n * n_groups, s));
   const int grid = n_cols < sm_count() * 2 ? n_cols : sm_count() * 2;
-  rank_sort_kernel<<<grid, 1024, 0, s>>>(d_scores, n, n_cols, keys, idx, d_positions, (unsigned long long*)d_borda);
+  rank_sort_kernel<<<grid, 1024, 0, s>>>(d_scores, n, n_cols, n_cols / n_groups, keys, idx, d_positions, (unsigned long long*)d_borda);
   N2V2R_CHECK_LAUNCH();
   return N2V2R_OK;
 }

@@ -50,7 +50,7 @@ static size_t carve(const n2v2r_uase_params_t* p, const StreamPlan& plan, void* 
   b->xs = a.take<__nv_bfloat16>(plan.xs_bytes / sizeof(__nv_bfloat16));
   b->parts = a.take<float>(plan.part_bytes / sizeof(float));
   b->partials = a.take<double>((size_t)kMaxParts * ll);
-  b->rpart = a.take<double>((size_t)sm_count() * 4 * p->l + 1024);
+  b->rpart = a.take<double>((size_t)kMaxParts * p->l + 1024);
   b->H = a.take<double>(ll); b->S = a.take<double>(ll); b->W = a.take<double>(ll);
   b->C = a.take<double>(ll); b->C2 = a.take<double>(ll); b->G = a.take<double>(ll);
   b->lam = a.take<double>(p->l); b->resid = a.take<double>(p->l);
@@ -118,7 +118,7 @@ extern "C" int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2
   auto cholqr_pass = [&](const float* X, float* dst) -> int {
     RC(launch_xty(s, X, X, n, l, b.partials, kMaxParts, b.G, 0));
     RC(launch_smallmat(s, 1, l, b.G, nullptr, nullptr, nullptr, b.C, nullptr, b.flag));
-    RC(launch_apply_small(s, X, n, l, b.C, l, l, dst, l, nullptr, nullptr, nullptr, nullptr, nullptr));
+    RC(launch_apply_small(s, X, n, l, b.C, l, l, dst, l));
     stats.kernel_launches += 4;
     return N2V2R_OK;
   };
@@ -168,10 +168,9 @@ extern "C" int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2
     // Rayleigh-Ritz on span(Q): H = Q^T M Q
     RC(launch_xty(s, b.Q, b.Y, n, l, b.partials, kMaxParts, b.H, 0));
     RC(launch_smallmat(s, 0, l, b.H, nullptr, b.W, b.lam, nullptr, nullptr, b.flag));
-    int n_parts = 0;
-    RC(launch_apply_small(s, b.Y, n, l, b.W, l, l, b.X1, l, b.Q, b.W, b.lam, b.rpart, &n_parts));   // X1 = Yw, residuals
-    RC(launch_sum_partials(s, b.rpart, n_parts, l, b.resid));
-    RC(launch_apply_small(s, b.Q, n, l, b.W, l, l, b.Qw, l, nullptr, nullptr, nullptr, nullptr, nullptr));  // Qw = Q W
+    RC(launch_apply_small(s, b.Y, n, l, b.W, l, l, b.X1, l));                                        // X1 = Yw = Y W
+    RC(launch_apply_small(s, b.Q, n, l, b.W, l, l, b.Qw, l));                                        // Qw = Q W
+    RC(launch_resid(s, b.X1, b.Qw, n, l, b.lam, b.rpart, kMaxParts, b.resid));                       // ||Yw - Qw Lam||^2 per column
     stats.kernel_launches += 6;
     N2V2R_CUDA(cudaMemcpyAsync(lam.data(), b.lam, sizeof(double) * l, cudaMemcpyDeviceToHost, s));
     N2V2R_CUDA(cudaMemcpyAsync(res.data(), b.resid, sizeof(double) * l, cudaMemcpyDeviceToHost, s));
@@ -255,8 +254,8 @@ extern "C" int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2
   // embeddings from the last Rayleigh-Ritz application: Z_t W Sigma^-1/2 ; left = Q W Sigma^1/2
   RC(launch_smallmat(s, 2, l, b.H, nullptr, b.W, b.lam, b.C, b.C2, b.flag));
   for (int t = 0; t < T; ++t)
-    RC(launch_apply_small(s, b.Z + t * nl, n, l, b.C, l, k, d_embed + (size_t)t * n * k, k, nullptr, nullptr, nullptr, nullptr, nullptr));
-  if (d_left) RC(launch_apply_small(s, b.Q, n, l, b.C2, l, k, d_left, k, nullptr, nullptr, nullptr, nullptr, nullptr));
+    RC(launch_apply_small(s, b.Z + t * nl, n, l, b.C, l, k, d_embed + (size_t)t * n * k, k));
+  if (d_left) RC(launch_apply_small(s, b.Q, n, l, b.C2, l, k, d_left, k));
   stats.kernel_launches += 1 + T + (d_left ? 1 : 0);
   N2V2R_CUDA(cudaEventRecord(ev_all1, s));
   N2V2R_CUDA(cudaStreamSynchronize(s));

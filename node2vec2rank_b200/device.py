@@ -302,15 +302,22 @@ def distances(emb: torch.Tensor, col_dims, col_metrics, strategy):
 
 
 def rank_borda(scores: torch.Tensor, want_positions=False):
-    """K10+K11: scores (n_cols, n) float64 -> (borda (n,) int64, positions (n_cols, n) int32 | None)."""
+    """K10+K11.  scores (n_cols, n) float64 -> (borda (n,) int64, positions (n_cols, n) int32 | None);
+    scores (G, n_cols, n) -> (borda (G, n), positions (G, n_cols, n) | None): all G comparisons in one launch."""
     lib = N.load()
-    n_cols, n = scores.shape
-    ws = torch.empty(lib.n2v2r_rank_workspace_bytes(n, n_cols), dtype=torch.uint8, device=scores.device)
-    borda = torch.empty(n, dtype=torch.int64, device=scores.device)
-    pos = torch.empty((n_cols, n), dtype=torch.int32, device=scores.device) if want_positions else None
-    N.check(lib.n2v2r_rank_borda(N.stream_ptr(), N.ptr(scores.contiguous()), n, n_cols, N.ptr(pos), N.ptr(borda),
-                                 N.ptr(ws), ws.numel()))
-    return borda, pos
+    grouped = scores.dim() == 3
+    G = scores.shape[0] if grouped else 1
+    n_cols, n = scores.shape[-2], scores.shape[-1]
+    scores = scores.contiguous()
+    ws = torch.empty(lib.n2v2r_rank_workspace_bytes(n, G * n_cols), dtype=torch.uint8, device=scores.device)
+    borda = torch.empty((G, n), dtype=torch.int64, device=scores.device)
+    pos = torch.empty((G, n_cols, n), dtype=torch.int32, device=scores.device) if want_positions else None
+    if G * n_cols > 0:
+        N.check(lib.n2v2r_rank_borda(N.stream_ptr(), N.ptr(scores), n, G * n_cols, G, N.ptr(pos), N.ptr(borda),
+                                     N.ptr(ws), ws.numel()))
+    if grouped:
+        return borda, pos
+    return borda[0], (pos[0] if pos is not None else None)
 
 
 def default_block_width(k, n):

@@ -54,7 +54,6 @@ class N2V2R:
         self.solver_info = None
         self._layers = None            # device-resident layers (built lazily, reused by DeDi)
         self._emb_dev = None
-        self._scores_dev = None
 
         if self.config["seed"]:        # falsy seed (None or 0) => unseeded, model.py:36
             random.seed(self.config["seed"])
@@ -129,13 +128,11 @@ class N2V2R:
         names, dims, mets = D.column_specs(self.embed_dimensions, self.distance_metrics)
         strategy = N.STRATEGIES[comp_strategy]
         scores = D.distances(self._emb_dev, dims, mets, strategy)        # (C, cols, n) float64
-        self._scores_dev = {}
         host = scores.cpu().numpy()
         for c in range(scores.shape[0]):
             key = str(c + 1)                                             # '1'..'T-1' or '1'..'T'
             table = pd.DataFrame(host[c].T, index=self.node_names, columns=names)
             pairwise_ranks_dict.setdefault(key, []).append(table)
-            self._scores_dev[key] = scores[c]
 
     def fit_transform_rank(self):
         """Differential scores of every node for every comparison: dict key -> DataFrame
@@ -170,17 +167,20 @@ class N2V2R:
             if self.config["verbose"] >= 0:
                 print("\nRank aggregation with Borda ...")
             dev = N.require_gpu()
-            for comparison_key in self.pairwise_ranks:
-                if method.casefold() != 'borda':
-                    raise NotImplementedError('Aggregation method not found. Available methods: Borda')
+            if method.casefold() != 'borda':
+                raise NotImplementedError('Aggregation method not found. Available methods: Borda')
+            keys = list(self.pairwise_ranks)
+            tables = []
+            for comparison_key in keys:
+                # always rank what the (user-visible, possibly edited) table holds, like model.py:171-175
                 table = self.pairwise_ranks[comparison_key]
-                cached = (self._scores_dev or {}).get(comparison_key)
-                if cached is not None and cached.shape == (table.shape[1], table.shape[0]):
-                    scores = cached
-                else:                                    # user-supplied / modified table
-                    scores = torch.from_numpy(np.ascontiguousarray(table.to_numpy(dtype=np.float64).T)).to(dev)
-                borda, _ = D.rank_borda(scores)
-                out[comparison_key] = pd.DataFrame(borda.cpu().numpy(), index=self.node_names, columns=['borda_ranks'])
+                tables.append(torch.from_numpy(np.array(table.to_numpy(dtype=np.float64).T, order="C")).to(dev))
+            if len({tuple(t.shape) for t in tables}) == 1:
+                bordas = D.rank_borda(torch.stack(tables))[0].cpu().numpy()          # every comparison in one launch
+            else:
+                bordas = [D.rank_borda(t)[0].cpu().numpy() for t in tables]
+            for comparison_key, borda in zip(keys, bordas):
+                out[comparison_key] = pd.DataFrame(borda, index=self.node_names, columns=['borda_ranks'])
             self.pairwise_aggregate_ranks = out
             exec_time_agg = round(time.time() - start_time, 2)
             if self.config["verbose"] == 1:

@@ -61,7 +61,7 @@ def test_no_gpu_fails_loudly(lib):
 def test_argument_validation_without_gpu(lib):
     """Entry points reject bad arguments before touching the device."""
     from node2vec2rank_b200 import _native as N
-    rc = lib.n2v2r_rank_borda(None, None, 10, 1, None, None, None, 0)
+    rc = lib.n2v2r_rank_borda(None, None, 10, 1, 1, None, None, None, 0)
     assert rc == N.EINVAL and b"null pointer" in lib.n2v2r_last_error()
     p = N.UaseParams(n=100, T_local=1, T_global=1, layer_offset=0, k=8, l=40, max_iters=10)
     assert lib.n2v2r_uase_workspace_bytes(ctypes.byref(p)) == 0

@@ -171,6 +171,19 @@ def test_rank_borda_golden_and_ties(gpu, golden_dir):
         assert borda.sum().item() == cols * n * (n + 1) // 2
 
 
+def test_rank_borda_grouped(gpu):
+    from node2vec2rank_b200 import device as D
+    rng = np.random.default_rng(6)
+    G, cols, n = 5, 22, 3001
+    s = rng.normal(size=(G, cols, n))
+    s[rng.random(s.shape) < 0.1] = 1.25
+    borda, pos = D.rank_borda(_t(s, gpu), want_positions=True)
+    assert borda.shape == (G, n) and pos.shape == (G, cols, n)
+    for g in range(G):
+        assert np.array_equal(borda[g].cpu().numpy(), port.borda_from_scores(s[g].T))
+    assert np.array_equal(pos[3, 7].cpu().numpy(), port.descending_positions(s[3, 7]))
+
+
 def test_borda_aggregate_parallel_mirror(gpu):
     from node2vec2rank_b200.model_utils import borda_aggregate_parallel
     rng = np.random.default_rng(8)

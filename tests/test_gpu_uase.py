@@ -71,7 +71,6 @@ def test_demo_end_to_end_vs_golden(gpu, demo, demo_graphs, tmp_path):
     # Borda bit-exact when fed the reference's own score table
     m.pairwise_ranks = {"1": ranks["1"].__class__(ref32, index=demo["ref_nodes"], columns=demo["ref_columns"])}
     m.node_names = demo["ref_nodes"]
-    m._scores_dev = None
     with contextlib.redirect_stdout(io.StringIO()):
         agg2 = m.aggregate_transform()
     assert np.array_equal(agg2["1"]["borda_ranks"].to_numpy(), port.borda_from_scores(ref32))
