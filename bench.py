@@ -343,7 +343,8 @@ def run_b200_arm(args):
                    "layers_per_gpu": len(mine), "l2_policy": "inputs larger than L2 (each layer pass streams >= 5 GB)",
                    "operator_applications": last["iterations"], "layer_passes": last["layer_passes"],
                    "outer_iterations": last["outer_iterations"], "converged": last["converged"],
-                   "angle_bound": last["angle_bound"], "setup_s": setup_s},
+                   "angle_bound": last["angle_bound"], "setup_s": setup_s,
+                   "solver_ms": last["total_ms"], "solver_stream_ms": last["stream_ms"], "solver_mma_ms": last["mma_ms"]},
         "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
     }
     print(json.dumps(line), flush=True)

@@ -102,6 +102,7 @@ extern "C" int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2
   double floor_mult = 0.02, rel_floor = 8.0 * (double)FLT_EPSILON;   // residual target: 8 eps32 lam_j (measured fp32 floor ~ eps32 lam_j)
   if (const char* ev = getenv("N2V2R_FLOOR_MULT")) floor_mult = atof(ev);     // developer knobs (scripts/probe_solver.py)
   if (const char* ev = getenv("N2V2R_REL_FLOOR")) rel_floor = atof(ev);
+  const bool trace = getenv("N2V2R_TRACE") != nullptr;
   const double rho_max = 1e4;            // cap on T_m(x_unlocked)/T_m(x_k): keeps every fp32 column dominated by its own Ritz vector
   n2v2r_uase_stats_t stats;
   memset(&stats, 0, sizeof(stats));
@@ -161,7 +162,7 @@ extern "C" int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2
   double bound = INFINITY;
   int locked = 0, outer = 0, stalls = 0;
   bool converged = false, stagnated = false, last_filtered = false;
-  double best_worst = INFINITY;
+  double best_worst = INFINITY, prev_worst = INFINITY, predicted_gain = 1.0;
   while (true) {
     ++outer;
     RC(apply_M(b.Q, b.Y, true));
@@ -200,12 +201,20 @@ extern "C" int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2
     while (locked < k && at_floor(locked)) ++locked;
     bool all_floor = true;
     for (int j = 0; j < k; ++j) all_floor = all_floor && at_floor(j);
-    // stagnation: two filtered outer iterations in a row without a 30 % drop of the worst residual ratio
+    // stagnation = the fp32 residual floor of this matrix is above the target.  After a filtered iteration:
+    //  (A) close to the target (worst <= 16) and the drop was < 1/30 of what the filter should have given, or
+    //  (B) worst <= 64 and the drop was < 2x, or (C) two filtered iterations in a row without a 30 % drop.
     double worst = 0.0;
     for (int j = 0; j < k; ++j) worst = std::max(worst, res[j] / target(j));
-    if (last_filtered && worst > 0.7 * best_worst) ++stalls; else if (worst <= 0.7 * best_worst) stalls = 0;
+    if (last_filtered) {
+      const double drop = prev_worst / std::max(worst, 1e-300);
+      if (worst <= 16.0 && drop < predicted_gain / 30.0) stagnated = true;
+      if (worst <= 64.0 && drop < 2.0) stagnated = true;
+      if (worst > 0.7 * best_worst) ++stalls; else stalls = 0;
+      if (stalls >= 2) stagnated = true;
+    }
     best_worst = std::min(best_worst, worst);
-    stagnated = stalls >= 2;
+    prev_worst = worst;
     converged = (bound <= p->tol) || all_floor || stagnated;
     last_filtered = false;
     if ((converged && stats.iterations >= p->min_iters) || stats.iterations >= p->max_iters) break;
@@ -221,12 +230,16 @@ extern "C" int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2
       if (m > 1) m = std::max(2, std::min(m, (int)std::min(need, 1e6)));
       m = std::min(m, p->max_iters - stats.iterations);
     }
+    if (trace)
+      fprintf(stderr, "[uase] outer %d apps %d locked %d bound %.3e worst %.3e lam1 %.4e lamk %.4e lam_l %.4e -> degree %d\n", outer,
+              stats.iterations, locked, bound, worst, lam[0], lam[k - 1], lam[l - 1], m);
     if (m <= 1) {                                            // plain subspace step: Q <- orth(M Qw)
       RC(cholqr_pass(b.X1, b.Qn));
       RC(cholqr_pass(b.Qn, b.Q));
       continue;
     }
     last_filtered = true;
+    predicted_gain = cheb_T((lam[k - 1] - c) / e, m);
     // X0 = Qw, X1 = (s1/e)(Yw - c Qw), then the three-term recurrence
     const double s1 = e / (lam_u - c);
     double sg = s1;
@@ -251,6 +264,9 @@ extern "C" int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2
     RC(cholqr_pass(x1, b.Qn));
     RC(cholqr_pass(b.Qn, b.Q));
   }
+  if (trace)
+    fprintf(stderr, "[uase] stop: outer %d apps %d locked %d bound %.3e converged %d stagnated %d\n", outer, stats.iterations, locked,
+            bound, (int)converged, (int)stagnated);
   // embeddings from the last Rayleigh-Ritz application: Z_t W Sigma^-1/2 ; left = Q W Sigma^1/2
   RC(launch_smallmat(s, 2, l, b.H, nullptr, b.W, b.lam, b.C, b.C2, b.flag));
   for (int t = 0; t < T; ++t)

@@ -117,3 +117,50 @@ def test_uase_argument_errors(gpu):
         D.uase([L], k=40, l=48)          # k >= n
     with pytest.raises(N.NativeError):
         D.uase([L], k=8, l=40)           # l not a multiple of 16
+
+
+def test_full_size_c2_properties(gpu):
+    """BASELINE configs[1] at full size (n = 20 000, 2 binarised layers): too large for the CPU oracle, so the
+    result is checked through size-independent properties: singular-pair residuals recomputed with the independent
+    SIMT product, orthonormality of the right factor, Borda checksums, and recovery of the planted signal."""
+    from node2vec2rank_b200 import _native as N
+    from node2vec2rank_b200 import device as D
+    from node2vec2rank_b200.synthetic import block_matrices
+    n, K, T, k, l = 20000, 32, 2, 24, 64
+    Bs, changed = block_matrices(K, T, seed=1)
+    layers = []
+    for t in range(T):
+        raw = D.sbm_generate(n, K, Bs[t], seed=1, layer=t)
+        layers.append(D.preprocess_to_layer(raw, binarize=True)[0])
+        del raw
+    assert all(L.n_planes == 1 and L.symmetric for L in layers)
+    dims = list(range(4, 25, 2))
+    emb, sigma, left, info = D.uase(layers, k, l=l, seed=42, check_dims=dims, want_left=True)
+    assert info["converged"] and info["iterations"] <= 40, info
+    assert np.all(np.diff(sigma) < 0)
+    # right factor: sum_t Y_t^T Y_t = diag(sigma) (V orthonormal, scaled by sqrt(sigma))
+    G = torch.einsum("tnd,tne->de", emb.double(), emb.double()).cpu().numpy()
+    assert np.allclose(np.diag(G), sigma, rtol=1e-5)
+    off = G - np.diag(np.diag(G))
+    assert np.abs(off).max() <= 1e-5 * sigma[0]
+    # singular-pair residuals with the independent SIMT kernel: M u_j = sigma_j^2 u_j, u_j = left_j / sqrt(sigma_j)
+    U = (left.double() / torch.from_numpy(np.sqrt(sigma)).to(gpu)).float()
+    pad = torch.zeros((n, l), dtype=torch.float32, device=gpu)
+    pad[:, :k] = U
+    MU = torch.zeros_like(pad)
+    for L in layers:
+        z = D.layer_apply(L, pad, transpose=True, algo=N.ALGO_SIMT)
+        MU += D.layer_apply(L, z, transpose=False, algo=N.ALGO_SIMT)
+    lam = torch.from_numpy(sigma ** 2).to(gpu)
+    r = (MU[:, :k].double() - U.double() * lam).norm(dim=0) / lam
+    assert float(r.max()) <= 2e-5, r
+    # ranking: Borda checksum and the planted signal (nodes of the communities whose block rows changed)
+    names, cd, cm = D.column_specs(dims, ["euclidean", "cosine"])
+    scores = D.distances(emb, cd, cm, N.SEQUENTIAL)
+    borda, pos = D.rank_borda(scores, want_positions=True)
+    assert borda.shape == (1, n) and int(borda.sum()) == 22 * n * (n + 1) // 2
+    p0 = pos[0, 0].cpu().numpy()
+    assert np.array_equal(np.sort(p0), np.arange(n))
+    planted = np.isin(np.arange(n) % K, changed[1])
+    top = np.argsort(-borda[0].cpu().numpy(), kind="stable")[: int(planted.sum())]
+    assert planted[top].mean() > 0.95
