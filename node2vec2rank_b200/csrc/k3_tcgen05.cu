@@ -91,6 +91,7 @@ struct StreamArgs {
   int n_planes, l, mh;              // planes, block width, 128-row halves per tile (1 or 2)
   int stages, n_tiles, n_splits, k_chunk;
   int n_jb;                         // column blocks of width l of the right operand (1 for the skinny products)
+  int upper_only;                   // SYRK: skip units entirely below the diagonal (projection)
   int64_t k_pad;                    // contraction length, multiple of 64
   int64_t rows_valid, cols_valid;   // extent of the output that may be written
   int64_t out_ld, split_stride;     // output leading dimension / elements between K-split partials
@@ -139,6 +140,7 @@ __global__ void __launch_bounds__(192, 1) stream_mma_kernel(const __grid_constan
         const int64_t k_begin = (int64_t)split * a.k_chunk;
         const int64_t k_end = (k_begin + a.k_chunk < a.k_pad) ? k_begin + a.k_chunk : a.k_pad;
         const int row0 = tile * 128 * a.mh;
+        if (a.upper_only && (jb + 1) * a.l <= row0) continue;
         for (int64_t k0 = k_begin; k0 < k_end; k0 += 64) {
           mbar_wait(bar_empty + 8 * stage, phase ^ 1u);
           const uint32_t base = smem0 + stage * a.stage_bytes;
@@ -154,7 +156,9 @@ __global__ void __launch_bounds__(192, 1) stream_mma_kernel(const __grid_constan
     // ===== MMA issuer =====
     int stage = 0; uint32_t phase = 0, uphase = 0;
     for (int u = blockIdx.x; u < n_units; u += gridDim.x) {
-      const int split = (u / a.n_tiles) / a.n_jb;
+      const int sj_ = u / a.n_tiles;
+      const int split = sj_ / a.n_jb;
+      if (a.upper_only && ((sj_ - split * a.n_jb) + 1) * a.l <= (u - sj_ * a.n_tiles) * 128 * a.mh) continue;
       const int64_t k_begin = (int64_t)split * a.k_chunk;
       const int64_t k_end = (k_begin + a.k_chunk < a.k_pad) ? k_begin + a.k_chunk : a.k_pad;
       mbar_wait(bar_tempty, uphase ^ 1u);            // epilogue has drained the accumulators
@@ -195,6 +199,7 @@ __global__ void __launch_bounds__(192, 1) stream_mma_kernel(const __grid_constan
     for (int u = blockIdx.x; u < n_units; u += gridDim.x) {
       const int sj = u / a.n_tiles, tile = u - sj * a.n_tiles;
       const int split = sj / a.n_jb, jb = sj - split * a.n_jb;
+      if (a.upper_only && (jb + 1) * a.l <= tile * 128 * a.mh) continue;
       mbar_wait(bar_tfull, uphase);
       tc_fence_after();
       for (int h = 0; h < a.mh; ++h) {
@@ -256,6 +261,31 @@ __global__ void __launch_bounds__(256) reduce_parts_kernel(const float* __restri
   reinterpret_cast<float4*>(out)[e4] = s;
 }
 
+
+// ---- projection epilogue: out[i][j] = out[j][i] = sum_s parts[s][i][j] for i <= j (fixed order; exactly symmetric) ----
+__global__ void __launch_bounds__(256) mirror_reduce_kernel(const float* __restrict__ parts, int n_splits, int64_t split_stride,
+                                                            int64_t m, float* __restrict__ out, int64_t ld_out) {
+  __shared__ float t[32][33];
+  const int bi = blockIdx.y, bj = blockIdx.x;
+  if (bi > bj) return;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  for (int r = ty; r < 32; r += 8) {
+    const int64_t i = (int64_t)bi * 32 + r, j = (int64_t)bj * 32 + tx;
+    float v = 0.f;
+    if (i < m && j < m) {
+      const int64_t ii = i <= j ? i : j, jj = i <= j ? j : i;      // diagonal tiles: read the upper element
+      for (int sp = 0; sp < n_splits; ++sp) v += parts[(size_t)sp * split_stride + ii * m + jj];
+      out[i * ld_out + j] = v;
+    }
+    t[r][tx] = v;
+  }
+  __syncthreads();
+  if (bi == bj) return;
+  for (int r = ty; r < 32; r += 8) {
+    const int64_t i = (int64_t)bj * 32 + r, j = (int64_t)bi * 32 + tx;       // out[j_orig][i_orig]
+    if (i < m && j < m) out[i * ld_out + j] = t[tx][r];
+  }
+}
 
 // ---- projection operand: W (r x c, f32/f64) -> Ws bf16 [3][m][k_pad], optionally transposed ------
 template <class T>
@@ -331,8 +361,9 @@ static int make_map(CUtensorMap* map, const void* base, int rank, const uint64_t
 // D[m_rows x (n_jb*l)] = A[m_rows x k] * B^T, A = n_planes planes (row stride lda), B = 3 split planes [3][b_rows][ldb]
 static int launch_mma(cudaStream_t s, const void* a_planes, int n_planes, int64_t m_rows, int64_t lda, size_t a_plane_stride,
                       const void* b_planes, int64_t b_rows, int64_t ldb, int l, int n_jb, int64_t k_pad, int k_chunk,
-                      float* out, int64_t out_ld, int64_t split_stride, int64_t rows_valid, int64_t cols_valid) {
+                      float* out, int64_t out_ld, int64_t split_stride, int64_t rows_valid, int64_t cols_valid, int upper_only = 0) {
   StreamArgs a;
+  a.upper_only = upper_only;
   a.n_planes = n_planes;
   a.l = l;
   a.mh = n_planes == 1 ? 2 : 1;
@@ -414,9 +445,13 @@ int stream_apply_tcgen05(cudaStream_t s, const StreamPlan& plan, const void* pla
 using namespace n2v2r;
 
 // K2: out = W^T W (on_rows=0) or W W^T (on_rows=1) -- preprocessing_utils.py:16-32
+static const int kProjChunk = 512;     // K-split of the projection: short fp32 accumulation chains in TMEM, partials summed in order
+
 extern "C" size_t n2v2r_project_workspace_bytes(int64_t rows, int64_t cols, int on_rows) {
   const int64_t m = on_rows ? rows : cols, k = on_rows ? cols : rows;
-  return align_up(sizeof(__nv_bfloat16) * 3 * (size_t)m * round_up(k, 64)) + 256;
+  const int64_t k_pad = round_up(k, 64);
+  const int64_t n_splits = (k_pad + kProjChunk - 1) / kProjChunk;
+  return align_up(sizeof(__nv_bfloat16) * 3 * (size_t)m * k_pad) + align_up(sizeof(float) * (size_t)n_splits * round_up(m, 256) * m) + 256;
 }
 
 extern "C" int n2v2r_project(void* stream, const void* d_W, int dtype, int64_t rows, int64_t cols, int64_t ld, int on_rows,
@@ -427,7 +462,10 @@ extern "C" int n2v2r_project(void* stream, const void* d_W, int dtype, int64_t r
   if (ws_bytes < n2v2r_project_workspace_bytes(rows, cols, on_rows)) { set_error("project: workspace too small"); return N2V2R_ENOMEM; }
   cudaStream_t s = (cudaStream_t)stream;
   const int64_t k_pad = round_up(k, 64);
+  const int n_splits = (int)((k_pad + kProjChunk - 1) / kProjChunk);
+  const int64_t m_pad = round_up(m, 256);
   __nv_bfloat16* Ws = (__nv_bfloat16*)d_ws;
+  float* parts = (float*)((char*)d_ws + align_up(sizeof(__nv_bfloat16) * 3 * (size_t)m * k_pad));
   dim3 grid((unsigned)((k_pad + 31) / 32), (unsigned)((m + 31) / 32));
   if (dtype == N2V2R_F32)
     split_planes_kernel<float><<<grid, 256, 0, s>>>((const float*)d_W, rows, cols, ld, on_rows ? 0 : 1, m, k_pad, Ws);
@@ -437,7 +475,12 @@ extern "C" int n2v2r_project(void* stream, const void* d_W, int dtype, int64_t r
   N2V2R_CHECK_LAUNCH();
   const int l = 64;
   const int n_jb = (int)((m + l - 1) / l);
-  // one K split: the contraction (the smaller bipartite side) is short
-  return launch_mma(s, Ws, 3, m, k_pad, (size_t)m * k_pad * sizeof(__nv_bfloat16), Ws, m, k_pad, l, n_jb, k_pad,
-                    (int)k_pad, d_out, ld_out, 0, m, m);
+  // SYRK: only units touching the upper triangle are computed; the mirror kernel fills the rest
+  int rc = launch_mma(s, Ws, 3, m, k_pad, (size_t)m * k_pad * sizeof(__nv_bfloat16), Ws, m, k_pad, l, n_jb, k_pad, kProjChunk,
+                      parts, m, m_pad * m, m, m, 1);
+  if (rc) return rc;
+  const unsigned tiles = (unsigned)((m + 31) / 32);
+  mirror_reduce_kernel<<<dim3(tiles, tiles), 256, 0, s>>>(parts, n_splits, m_pad * m, m, d_out, ld_out);
+  N2V2R_CHECK_LAUNCH();
+  return N2V2R_OK;
 }

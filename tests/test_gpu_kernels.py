@@ -67,6 +67,26 @@ def test_percentile_cut_matches_numpy(gpu, dtype, keep):
         assert got == ref and type(got) == type(ref), (dtype, keep, absolute, thr, got, ref)
 
 
+@pytest.mark.parametrize("shape", [(300, 1200), (1111, 257), (64, 4100)])
+def test_projection_vs_fp64(gpu, shape):
+    """K2 (preprocessing_utils.py:16-32): W^T W / W W^T.  The reference multiplies in float64 and casts to float32;
+    the tensor-core path carries 24-bit operands and accumulates in fp32 (truncating adder, 512-long chains):
+    tolerance 4e-6 of the largest entry, output exactly symmetric."""
+    from node2vec2rank_b200.preprocessing_utils import bipartite_to_unipartite_projection
+    rng = np.random.default_rng(shape[0])
+    W = rng.normal(size=shape) + 0.5
+    for on in ("columns", "rows", "Rows"):
+        out = bipartite_to_unipartite_projection(W, on)
+        ref = port.bipartite_to_unipartite_projection(W, on)
+        assert out.shape == ref.shape and out.dtype == np.float32
+        assert np.abs(out - ref).max() <= 4e-6 * np.abs(ref).max()
+        assert np.array_equal(out, out.T)
+    with pytest.raises(ValueError):
+        bipartite_to_unipartite_projection(W, "diagonal")
+    with pytest.raises(AssertionError):
+        bipartite_to_unipartite_projection(np.eye(5), "rows")
+
+
 def test_transform_planes_colsum_and_symmetry(gpu):
     from node2vec2rank_b200 import device as D
     rng = np.random.default_rng(9)
