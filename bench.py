@@ -41,6 +41,13 @@ WORKLOADS = {
     # BASELINE.json configs[1]
     "c2": dict(n=20000, T=2, K=32, weighted=False, keep=100, binarize=True, strategy="sequential",
                name="synthetic 2-layer dense SBM n=20k, binarize, sequential, d=4..24, euclidean+cosine, Borda"),
+    # BASELINE.json configs[3]: bipartite layers -> W^T W on the tensor cores (K2) -> UASE; the projection is inside the step
+    "c4": dict(n=30000, rows=2000, T=2, K=32, weighted=True, keep=100, binarize=False, strategy="sequential", bipartite=True,
+               name="bipartite PANDA-shaped 2-layer graph (2k x 30k), project_unipartite_on=columns (W^T W, tcgen05), UASE d=4..24, "
+                    "euclidean+cosine, Borda"),
+    # BASELINE.json configs[4]: stability run, seeds sharded over the ranks, layers replicated
+    "c5": dict(n=30000, T=4, K=32, weighted=False, keep=100, binarize=True, strategy="sequential", seeds=list(range(16)),
+               name="stability run: 16 seeds x 4-layer SBM n=30k, binarize, sequential, d=4..24, euclidean+cosine, Borda across runs"),
 }
 CPU_SAMPLE_N = 3000
 GRAPH_SEED = 1
@@ -160,24 +167,33 @@ def run_reference_arm(args):
     if rank != 0:
         return 0
     w = workload_of(args)
-    n_s = min(CPU_SAMPLE_N, w["n"])
-    graphs = cpu_sample_graphs(w, n_s)
-    for _ in range(args.warmup):
-        cpu_step(graphs, w)
-    t0 = time.perf_counter()
-    parts = [cpu_step(graphs, w) for _ in range(args.steps)]
-    dt = (time.perf_counter() - t0) / max(args.steps, 1)
-    full = scale_to_full(dt, w, n_s)
-    sample = (f"n={n_s} of {w['n']} nodes, all {w['T']} layers, same transform/sweep; measured {dt:.2f} s/step "
-              f"(fit {np.mean([p['fit'] for p in parts]):.2f}, distances {np.mean([p['distances'] for p in parts]):.2f}, "
-              f"borda {np.mean([p['borda'] for p in parts]):.2f}); value = measured x (n_full/n_sample)^2, linear in matrix "
-              f"entries -- a lower bound, the reference's fit grows ~n^2.4")
+    if w.get("bipartite"):
+        for _ in range(args.warmup):
+            cpu_c4_leg(w)
+        legs = [cpu_c4_leg(w) for _ in range(max(args.steps, 1))]
+        full, dt, sample = float(np.mean([x["value"] for x in legs])), float(np.mean([x["sample_seconds"] for x in legs])), legs[-1]["sample"]
+        cores = legs[-1]["cores"]
+    else:
+        n_s = min(CPU_SAMPLE_N, w["n"])
+        runs = len(w.get("seeds", [0]))
+        graphs = cpu_sample_graphs(w, n_s)
+        for _ in range(args.warmup):
+            cpu_step(graphs, w)
+        t0 = time.perf_counter()
+        parts = [cpu_step(graphs, w) for _ in range(args.steps)]
+        dt = (time.perf_counter() - t0) / max(args.steps, 1)
+        full = scale_to_full(dt, w, n_s) * runs
+        cores = cpu_cores_used()
+        sample = (f"n={n_s} of {w['n']} nodes, all {w['T']} layers, same transform/sweep, one run of {runs}; measured {dt:.2f} s/step "
+                  f"(fit {np.mean([p['fit'] for p in parts]):.2f}, distances {np.mean([p['distances'] for p in parts]):.2f}, "
+                  f"borda {np.mean([p['borda'] for p in parts]):.2f}); value = measured x (n_full/n_sample)^2 x runs, linear in matrix "
+                  f"entries -- a lower bound, the reference's fit grows ~n^2.4")
     line = {
         "impl": "reference", "metric": "UASE sweep+rank wall time", "value": full, "unit": "s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": full * 1e3, "higher_is_better": False, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": w["name"], "n": w["n"], "layers": w["T"], "communities": w["K"]},
-        "cpu_baseline": {"value": full, "unit": "s", "cores": cpu_cores_used(), "kind": "port", "sample": sample,
+        "cpu_baseline": {"value": full, "unit": "s", "cores": cores, "kind": "port", "sample": sample,
                          "sample_seconds": dt},
         "e2e": {"value": full, "unit": "s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -187,7 +203,94 @@ def run_reference_arm(args):
 
 
 # ---- B200 arm ------------------------------------------------------------------------------------
+class Env:
+    """One process per GPU: device, rendezvous, barrier and max-over-ranks (torch.distributed over NCCL)."""
+
+    def __init__(self):
+        import torch
+        import torch.distributed as tdist
+        from node2vec2rank_b200 import _native as N
+        self.torch, self.tdist = torch, tdist
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+        torch.cuda.set_device(self.local_rank)
+        self.dev = N.require_gpu()
+        if self.world > 1:
+            tdist.init_process_group("nccl", device_id=self.dev)
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except (OSError, ValueError):
+            pass
+        self.hbm_peak, self.hbm_src = (float(peaks["hbm_gbs"]), "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
+        key = "bf16_tflops_sustained" if "bf16_tflops_sustained" in peaks else "bf16_tflops"
+        self.tc_peak, self.tc_src = (float(peaks[key]), f"measured ({key})") if key in peaks else (1394.0, "fallback")
+
+    def barrier(self):
+        if self.world > 1:
+            self.tdist.barrier()
+        self.torch.cuda.synchronize()
+
+    def reduce_max(self, x):
+        if self.world == 1:
+            return x
+        t = self.torch.tensor([x], dtype=self.torch.float64, device=self.dev)
+        self.tdist.all_reduce(t, op=self.tdist.ReduceOp.MAX)
+        return float(t.item())
+
+    def timed(self, step, steps, warmup):
+        """W untimed steps, then exactly K steps between barrier + synchronize, CUDA events, max over ranks.
+        Returns (ms per step, list of step results, clocks dict on rank 0)."""
+        torch = self.torch
+        for _ in range(warmup):
+            step()
+        sampler = ClockSampler(self.local_rank)
+        if self.rank == 0:
+            sampler.start()
+        self.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        results = [step() for _ in range(steps)]
+        e1.record()
+        self.barrier()
+        ms = self.reduce_max(e0.elapsed_time(e1) / max(steps, 1))
+        return ms, results, (sampler.stop() if self.rank == 0 else None)
+
+    def timed_host(self, step, steps, warmup):
+        """The end-to-end leg: wall clock around K calls of the public API (host buffers in, host tables out)."""
+        for _ in range(warmup):
+            step()
+        self.barrier()
+        t0 = time.perf_counter()
+        out = None
+        for _ in range(steps):
+            out = step()
+        self.barrier()
+        return self.reduce_max((time.perf_counter() - t0) / max(steps, 1)), out
+
+    def finish(self):
+        if self.world > 1:
+            self.tdist.destroy_process_group()
+
+
+def cpu_baseline_leg(w, n, T):
+    n_s = min(CPU_SAMPLE_N, n)
+    g = cpu_sample_graphs(w, n_s)
+    tm = cpu_step(g, w)
+    runs = len(w.get("seeds", [0]))
+    return {"value": scale_to_full(tm["total"], w, n_s) * runs, "unit": "s", "cores": cpu_cores_used(), "kind": "port",
+            "sample": f"n={n_s} of {n} nodes, all {T} layers, one run of {runs}; measured {tm['total']:.2f} s (fit {tm['fit']:.2f}, distances "
+                      f"{tm['distances']:.2f}, borda {tm['borda']:.2f}); value = measured x (n_full/n_sample)^2 x runs (lower bound)",
+            "sample_seconds": tm["total"]}
+
+
 def run_b200_arm(args):
+    w = workload_of(args)
+    if w.get("bipartite"):
+        return run_b200_c4(args, w)
+    if w.get("seeds"):
+        return run_b200_c5(args, w)
     import torch
     import torch.distributed as tdist
     from node2vec2rank_b200 import _native as N
@@ -195,35 +298,15 @@ def run_b200_arm(args):
     from node2vec2rank_b200 import dist as ND
     from node2vec2rank_b200.model import N2V2R
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    torch.cuda.set_device(local_rank)
-    dev = N.require_gpu()
-    if world > 1:
-        tdist.init_process_group("nccl", device_id=dev)
-    w = workload_of(args)
+    env = Env()
+    world, rank, local_rank, dev = env.world, env.rank, env.local_rank, env.dev
+    barrier, reduce_max = env.barrier, env.reduce_max
+    hbm_peak, peak_src = env.hbm_peak, env.hbm_src
     n, T, K, l = w["n"], w["T"], w["K"], args.block_width
+    if world > T:
+        raise SystemExit(f"workload {args.workload} has {T} layers: at most {T} ranks (row-slab sharding is not implemented)")
     mine = ND.layer_partition(T, world, rank)
     Bs = block_probabilities(w)
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-    except (OSError, ValueError):
-        pass
-    hbm_peak, peak_src = (float(peaks["hbm_gbs"]), "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
-
-    def barrier():
-        if world > 1:
-            tdist.barrier()
-        torch.cuda.synchronize()
-
-    def reduce_max(x):
-        if world == 1:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device=dev)
-        tdist.all_reduce(t, op=tdist.ReduceOp.MAX)
-        return float(t.item())
 
     # ---- setup (untimed): K0 generate + K1 load pass per local layer -------------------------------
     t_setup = time.perf_counter()
@@ -273,22 +356,7 @@ def run_b200_arm(args):
     clocks = sampler.stop() if rank == 0 else None
 
     # ---- roofline of the dominant kernel (tcgen05 streaming product), measured live in the timed steps ----
-    mma_ms = sum(i["mma_ms"] for i in infos)
-    mma_n = sum(i["mma_launches"] for i in infos)
-    alg_bytes = float(n) * n * 2.0 * n_planes + 4.0 * l * 2.0 * n          # matrix once + skinny in + skinny out
-    achieved = alg_bytes / (mma_ms / max(mma_n, 1) * 1e-3) / 1e9 if mma_n else 0.0
-    stream_ms = sum(i["stream_ms"] for i in infos)
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
-                "traffic": None, "kernel": "stream_mma_kernel", "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": alg_bytes, "launches_per_step": mma_n / max(args.steps, 1),
-                "avg_launch_ms": mma_ms / max(mma_n, 1), "share_of_step": mma_ms / max(ms_step * args.steps, 1e-9),
-                "streaming_products_share_of_step": stream_ms / max(ms_step * args.steps, 1e-9)}
-    traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(traffic_file):
-        try:
-            roofline["traffic"] = json.load(open(traffic_file)).get(f"{args.workload}_bytes_per_launch")
-        except ValueError:
-            pass
+    roofline = stream_roofline(env, infos, ms_step, args.steps, n, n_planes, l, args.workload)
 
     # ---- e2e: the public API on host buffers ------------------------------------------------------------
     e2e = None
@@ -320,19 +388,10 @@ def run_b200_arm(args):
                "api": "N2V2R(graphs=float32 host arrays).fit_transform_rank() + aggregate_transform()"}
 
     if rank != 0:
-        if world > 1:
-            tdist.destroy_process_group()
+        env.finish()
         return 0
     # ---- cpu_baseline (rank 0, N = 1 only) -------------------------------------------------------------
-    cpu = None
-    if world == 1 and not args.no_cpu:
-        n_s = min(CPU_SAMPLE_N, n)
-        g = cpu_sample_graphs(w, n_s)
-        tm = cpu_step(g, w)
-        cpu = {"value": scale_to_full(tm["total"], w, n_s), "unit": "s", "cores": cpu_cores_used(), "kind": "port",
-               "sample": f"n={n_s} of {n} nodes, all {T} layers, one step; measured {tm['total']:.2f} s (fit {tm['fit']:.2f}, distances "
-                         f"{tm['distances']:.2f}, borda {tm['borda']:.2f}); value = measured x (n_full/n_sample)^2 (lower bound)",
-               "sample_seconds": tm["total"]}
+    cpu = cpu_baseline_leg(w, n, T) if (world == 1 and not args.no_cpu) else None
     last = infos[-1]
     line = {
         "metric": "UASE sweep+rank wall time", "value": ms_step / 1e3, "unit": "s", "n_gpus": world, "steps": args.steps,
@@ -348,9 +407,222 @@ def run_b200_arm(args):
         "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
     }
     print(json.dumps(line), flush=True)
-    if world > 1:
-        tdist.destroy_process_group()
+    env.finish()
     return 0
+
+
+def stream_roofline(env, infos, ms_step, steps, n, n_planes, l, workload):
+    """Roofline of the tcgen05 streaming product, from the per-launch CUDA-event times the solver records."""
+    mma_ms = sum(i["mma_ms"] for i in infos)
+    mma_n = sum(i["mma_launches"] for i in infos)
+    alg_bytes = float(n) * n * 2.0 * n_planes + 4.0 * l * 2.0 * n          # SURVEY 8d: matrix once + skinny in + skinny out
+    achieved = alg_bytes / (mma_ms / max(mma_n, 1) * 1e-3) / 1e9 if mma_n else 0.0
+    stream_ms = sum(i["stream_ms"] for i in infos)
+    roof = {"bound": "hbm", "achieved": achieved, "peak": env.hbm_peak, "unit": "GB/s", "frac": achieved / env.hbm_peak,
+            "traffic": None, "kernel": "stream_mma_kernel", "peak_source": env.hbm_src,
+            "algorithmic_bytes_per_launch": alg_bytes, "launches_per_step": mma_n / max(steps, 1),
+            "avg_launch_ms": mma_ms / max(mma_n, 1), "share_of_step": mma_ms / max(ms_step * steps, 1e-9),
+            "streaming_products_share_of_step": stream_ms / max(ms_step * steps, 1e-9)}
+    try:
+        roof["traffic"] = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(f"{workload}_bytes_per_launch")
+    except (OSError, ValueError):
+        pass
+    return roof
+
+
+def run_b200_c5(args, w):
+    """BASELINE configs[4]: S seeds x one UASE run each on the same resident layers, Borda across runs.
+    Seeds are split over the ranks (every rank holds all layers); score tables are all-gathered."""
+    import torch
+    from node2vec2rank_b200 import _native as N
+    from node2vec2rank_b200 import device as D
+    from node2vec2rank_b200 import dist as ND
+    from node2vec2rank_b200.stability import StabilityRun
+
+    env = Env()
+    n, T, K, l, seeds = w["n"], w["T"], w["K"], args.block_width, w["seeds"]
+    mine = [seeds[i] for i in ND.layer_partition(len(seeds), env.world, env.rank)]
+    Bs = block_probabilities(w)
+    t_setup = time.perf_counter()
+    layers, host_graphs = [], []
+    for t in range(T):
+        raw = D.sbm_generate(n, K, Bs[t], seed=GRAPH_SEED, layer=t, weighted=w["weighted"])
+        layer, f32 = D.preprocess_to_layer(raw, top_percent_keep=w["keep"], binarize=w["binarize"], want_f32=not args.no_e2e)
+        del raw
+        if f32 is not None:
+            h = torch.empty((n, n), dtype=torch.float32, pin_memory=True)
+            h.copy_(f32)
+            host_graphs.append(h.numpy())
+            del f32
+        layers.append(layer)
+    torch.cuda.synchronize()
+    setup_s = time.perf_counter() - t_setup
+    names, cdims, cmets = D.column_specs(DIMS, METRICS)
+    strategy = N.STRATEGIES[w["strategy"]]
+
+    def step():
+        infos, local = [], []
+        for seed in mine:
+            emb, _, _, info = D.uase(layers, max(DIMS), l=l, tol=1e-5, max_iters=400, seed=seed, check_dims=DIMS)
+            infos.append(info)
+            local.append(D.distances(emb, cdims, cmets, strategy))
+        sc = torch.stack(local) if local else torch.empty((0, T - 1, len(cdims), n), dtype=torch.float64, device=env.dev)
+        if env.world > 1:
+            sc = ND.gather_blocks(sc, len(seeds))
+        S, C, cols, _ = sc.shape
+        borda = D.rank_borda(sc.permute(1, 0, 2, 3).reshape(C, S * cols, n))[0]
+        return infos, borda, sum(i["kernel_launches"] + 1 for i in infos) + 1
+
+    ms_step, results, clocks = env.timed(step, args.steps, args.warmup)
+    infos = [i for r in results for i in r[0]]
+    launches = sum(r[2] for r in results)
+    roofline = stream_roofline(env, infos, ms_step, args.steps, n, layers[0].n_planes, l, args.workload)
+    e2e = None
+    if not args.no_e2e:
+        del layers
+        torch.cuda.empty_cache()
+        cfg = dict(embed_dimensions=DIMS, distance_metrics=METRICS, comp_strategy=w["strategy"], seed=None, save_dir=None,
+                   verbose=-1, block_width=l, seed_sharded=env.world > 1)
+
+        def e2e_step():
+            run = StabilityRun(graphs=host_graphs, nodes=np.arange(n), config=cfg, seeds=seeds)
+            agg = run.run()                       # H2D of the graphs, plane build, all solves, Borda across runs, D2H of the tables
+            return sum(v.shape[0] * v.shape[1] * 8 for v in run.pairwise_ranks.values()) + sum(v.shape[0] * 8 for v in agg.values()) \
+                + sum(v.shape[0] * v.shape[1] * 8 for v in run.per_seed_aggregate_ranks.values())
+
+        e2e_s, d2h = env.timed_host(e2e_step, args.steps, min(args.warmup, 1))
+        e2e = {"value": e2e_s, "unit": "s", "h2d_bytes_per_step": int(T) * n * n * 4, "d2h_bytes_per_step": int(d2h),
+               "api": "StabilityRun(graphs=float32 host arrays, seeds).run()"}
+    if env.rank != 0:
+        env.finish()
+        return 0
+    cpu = cpu_baseline_leg(w, n, T) if (env.world == 1 and not args.no_cpu) else None
+    line = {
+        "metric": "UASE sweep+rank wall time", "value": ms_step / 1e3, "unit": "s", "n_gpus": env.world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": False, "scaling": "strong", "vs_baseline": None,
+        "dtype": "bf16 planes x3-split bf16 operand, fp32 accumulate (tcgen05), fp64 small dense", "data": "synthetic",
+        "config": {"workload": w["name"], "n": n, "layers": T, "communities": K, "block_width": l, "seeds": len(seeds),
+                   "seeds_per_gpu": len(mine), "planes_per_layer": 1, "l2_policy": "inputs larger than L2 (each layer pass streams 1.8 GB)",
+                   "operator_applications_per_run": [i["iterations"] for i in results[-1][0]],
+                   "all_converged": all(i["converged"] for i in infos), "setup_s": setup_s},
+        "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+    }
+    print(json.dumps(line), flush=True)
+    env.finish()
+    return 0
+
+
+def run_b200_c4(args, w):
+    """BASELINE configs[3]: two bipartite layers (2k x 30k) -> W^T W on the tensor cores (K2) -> cut -> planes ->
+    UASE -> rank.  The projection is inside the step; its roofline is the tensor pipe."""
+    import torch
+    from node2vec2rank_b200 import _native as N
+    from node2vec2rank_b200 import device as D
+    from node2vec2rank_b200.model import N2V2R
+    from node2vec2rank_b200.preprocessing_utils import network_transform_device
+    from node2vec2rank_b200.synthetic import bipartite_layer_numpy
+
+    env = Env()
+    if env.world > 1:
+        raise SystemExit("workload c4 is a one-GPU configuration (BASELINE configs[3])")
+    n, r, T, K, l = w["n"], w["rows"], w["T"], w["K"], args.block_width
+    t_setup = time.perf_counter()
+    hosts = []
+    for t in range(T):
+        h = torch.empty((r, n), dtype=torch.float32, pin_memory=True)
+        h.copy_(torch.from_numpy(bipartite_layer_numpy(r, n, K, GRAPH_SEED, t)))
+        hosts.append(h)
+    Ws = [h.to(env.dev) for h in hosts]
+    torch.cuda.synchronize()
+    setup_s = time.perf_counter() - t_setup
+    names, cdims, cmets = D.column_specs(DIMS, METRICS)
+    strategy = N.STRATEGIES[w["strategy"]]
+    proj_events = []
+
+    def step():
+        layers = []
+        for W in Ws:
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            P = D.project(W, "columns")
+            b.record()
+            proj_events.append((a, b))
+            layers.append(D.preprocess_to_layer(P, top_percent_keep=w["keep"])[0])
+            del P
+        emb, _, _, info = D.uase(layers, max(DIMS), l=l, tol=1e-5, max_iters=400, seed=SOLVER_SEED, check_dims=DIMS)
+        scores = D.distances(emb, cdims, cmets, strategy)
+        borda = D.rank_borda(scores)[0]
+        info["n_planes"] = layers[0].n_planes
+        return info, borda, info["kernel_launches"] + 2 + T * 12
+
+    ms_step, results, clocks = env.timed(step, args.steps, args.warmup)
+    infos = [x[0] for x in results]
+    launches = sum(x[2] for x in results)
+    timed_events = proj_events[-args.steps * T:]
+    proj_ms = float(np.mean([a.elapsed_time(b) for a, b in timed_events]))
+    flop = 2.0 * r * n * n
+    achieved = flop / (proj_ms * 1e-3) / 1e12
+    roofline = {"bound": "tensor", "achieved": achieved, "peak": env.tc_peak, "unit": "TFLOP/s", "frac": achieved / env.tc_peak,
+                "traffic": None, "kernel": "stream_mma_kernel (SYRK mode) + split_planes_kernel + mirror_reduce_kernel",
+                "peak_source": env.tc_src, "algorithmic_flop_per_launch": flop, "launches_per_step": T, "avg_launch_ms": proj_ms,
+                "share_of_step": proj_ms * T / ms_step,
+                "note": "algorithmic 2*r*c*n_out FLOP of the full product; the kernel issues 6 bf16 MMA terms (3x3 split, 6 kept) on "
+                        "the upper triangle only, i.e. 3x the algorithmic MMA work",
+                "streaming_products": stream_roofline(env, infos, ms_step, args.steps, n, infos[-1]["n_planes"], l, args.workload)}
+    e2e = None
+    if not args.no_e2e:
+        del Ws
+        torch.cuda.empty_cache()
+        cfg = dict(embed_dimensions=DIMS, distance_metrics=METRICS, comp_strategy=w["strategy"], seed=SOLVER_SEED, save_dir=None,
+                   verbose=-1, block_width=l)
+
+        def e2e_step():
+            graphs = [network_transform_device(h.numpy(), top_percent_keep=w["keep"], project_unipartite_on="columns")[0] for h in hosts]
+            m = N2V2R(graphs=graphs, nodes=np.arange(n), config=cfg)
+            ranks = m.fit_transform_rank()
+            agg = m.aggregate_transform()
+            return T * n * max(DIMS) * 4 + sum(v.shape[0] * v.shape[1] * 8 for v in ranks.values()) + sum(v.shape[0] * 8 for v in agg.values())
+
+        e2e_s, d2h = env.timed_host(e2e_step, args.steps, args.warmup)
+        e2e = {"value": e2e_s, "unit": "s", "h2d_bytes_per_step": T * r * n * 4, "d2h_bytes_per_step": int(d2h),
+               "api": "network_transform_device(host float32 bipartite, project_unipartite_on='columns') + N2V2R(...).fit_transform_rank() "
+                      "+ aggregate_transform()"}
+    cpu = None
+    if not args.no_cpu:
+        cpu = cpu_c4_leg(w)
+    last = infos[-1]
+    line = {
+        "metric": "UASE sweep+rank wall time", "value": ms_step / 1e3, "unit": "s", "n_gpus": 1, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": False, "scaling": "strong", "vs_baseline": None,
+        "dtype": "projection: 3x3 split-bf16 (6 terms) fp32 accumulate (tcgen05); solve: bf16 planes x3-split operand; fp64 small dense",
+        "data": "synthetic",
+        "config": {"workload": w["name"], "n": n, "bipartite_rows": r, "layers": T, "communities": K, "block_width": l,
+                   "planes_per_layer": last["n_planes"], "l2_policy": "inputs larger than L2 (each projected layer is 3.6 GB fp32)",
+                   "operator_applications": last["iterations"], "layer_passes": last["layer_passes"], "converged": last["converged"],
+                   "angle_bound": last["angle_bound"], "projection_ms_per_layer": proj_ms, "solver_ms": last["total_ms"], "setup_s": setup_s},
+        "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+    }
+    print(json.dumps(line), flush=True)
+    env.finish()
+    return 0
+
+
+def cpu_c4_leg(w, cols_sample=4000):
+    """The reference's path on a bounded C4 sample: float64 W^T W (np.matmul, all BLAS threads) + transform + fit/rank/Borda
+    at n = cols_sample; scaled by (n/n_s)^2 for everything quadratic in n (a lower bound for the fit)."""
+    from node2vec2rank_b200.synthetic import bipartite_layer_numpy
+    from oracle import reference_port as port
+    r, n = w["rows"], w["n"]
+    t0 = time.perf_counter()
+    graphs = [port.network_transform(bipartite_layer_numpy(r, cols_sample, w["K"], GRAPH_SEED, t).astype(np.float64),
+                                     top_percent_keep=w["keep"], project_unipartite_on="columns") for t in range(w["T"])]
+    t1 = time.perf_counter()
+    tm = cpu_step(graphs, w)
+    total = (t1 - t0) + tm["total"]
+    return {"value": total * (n / cols_sample) ** 2, "unit": "s", "cores": os.cpu_count() or 1, "kind": "port",
+            "sample": f"{r} x {cols_sample} of {r} x {n} per layer; measured {total:.2f} s (projection+transform {t1 - t0:.2f}, fit {tm['fit']:.2f}, "
+                      f"distances {tm['distances']:.2f}, borda {tm['borda']:.2f}); value = measured x (n_full/n_sample)^2 (lower bound)",
+            "sample_seconds": total}
 
 
 def main():

@@ -79,4 +79,12 @@ def gather_layers(local: torch.Tensor, T, group=None):
     return torch.cat([o[:c] for o, c in zip(out, counts)], dim=0)
 
 
-__all__ = ["is_distributed", "layer_partition", "make_allreduce_callback", "gather_layers"]
+def gather_blocks(local: torch.Tensor, total, group=None):
+    """gather_layers for blocks with any number of trailing dimensions: (B_local, ...) -> (total, ...),
+    the blocks split over the ranks by layer_partition (used for the seeds of a stability run)."""
+    tail = tuple(local.shape[1:])
+    flat = local.reshape(local.shape[0], 1, -1) if local.shape[0] else local.new_zeros((0, 1, int(torch.Size(tail).numel())))
+    return gather_layers(flat, total, group).reshape((total,) + tail)
+
+
+__all__ = ["is_distributed", "layer_partition", "make_allreduce_callback", "gather_layers", "gather_blocks"]

@@ -320,6 +320,24 @@ def fit_rank_borda(graphs, embed_dimensions, distance_metrics, comp_strategy,
     return emb, ranks, borda
 
 
+def stability_borda(graphs, embed_dimensions, distance_metrics, comp_strategy, seeds, dtype=None):
+    """README.md:54,173 -- "running it multiple times and aggregating": one fit_transform_rank
+    (model.py:98-147) per seed (model.py:36-38 seeds np.random, which is svds' start vector),
+    all runs' columns concatenated per comparison (seeds outer), then aggregate_transform's Borda
+    (model.py:149-201) over the union.  Returns ({key: (names, scores (n, S*C))}, {key: borda})."""
+    union = {}
+    for seed in seeds:
+        np.random.seed(seed)
+        _, ranks, _ = fit_rank_borda(graphs, embed_dimensions, distance_metrics, comp_strategy,
+                                     faithful=False, dtype=dtype)
+        for key, (names, scores) in ranks.items():
+            u = union.setdefault(key, ([], []))
+            u[0].extend(f"seed-{seed}_{c}" for c in names)
+            u[1].append(scores)
+    tables = {key: (names, np.concatenate(blocks, axis=1)) for key, (names, blocks) in union.items()}
+    return tables, {key: borda_from_scores(t[1]) for key, t in tables.items()}
+
+
 # --------------------------------------------------------------------------------------
 # parity measures (SURVEY Appendix A)
 # --------------------------------------------------------------------------------------

@@ -46,6 +46,13 @@ def _worker(rank, world, port, q):
         assert torch.equal(got, full)
         with pytest.raises(ValueError):
             ND.gather_layers(full[:0].clone() if rank == 0 else full[:3].clone(), T)
+        # seeds of a stability run: 3 seeds over 2 ranks, score blocks (S_local, C, cols, n); a rank may hold none
+        S, Cc, cols = 3, 2, 4
+        sc = torch.arange(S * Cc * cols * n, dtype=torch.float64).reshape(S, Cc, cols, n)
+        sm = ND.layer_partition(S, world, rank)
+        assert torch.equal(ND.gather_blocks(sc[sm.start:sm.stop].clone(), S), sc)
+        one = ND.layer_partition(1, world, rank)
+        assert torch.equal(ND.gather_blocks(sc[one.start:one.stop].clone(), 1), sc[:1])
         tdist.barrier()
         tdist.destroy_process_group()
         q.put((rank, "ok"))

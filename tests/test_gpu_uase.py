@@ -164,3 +164,39 @@ def test_full_size_c2_properties(gpu):
     planted = np.isin(np.arange(n) % K, changed[1])
     top = np.argsort(-borda[0].cpu().numpy(), kind="stable")[: int(planted.sum())]
     assert planted[top].mean() > 0.95
+
+
+def test_c4_shaped_pipeline_vs_oracle(gpu):
+    """BASELINE configs[3] in miniature: bipartite layers -> W^T W (K2, tcgen05) -> cut -> planes -> UASE -> scores,
+    against the oracle's network_transform (float64 np.matmul) + fp64 dense SVD.  Every cut 2..12 has a gap here."""
+    from node2vec2rank_b200 import _native as N
+    from node2vec2rank_b200 import device as D
+    from node2vec2rank_b200.preprocessing_utils import network_transform, network_transform_device
+    from node2vec2rank_b200.synthetic import bipartite_layer_numpy
+    r, c, K, k = 160, 1200, 8, 12
+    Ws = [bipartite_layer_numpy(r, c, K, 4, t) for t in range(2)]
+    ref_graphs = [port.network_transform(W.astype(np.float64), top_percent_keep=60, project_unipartite_on="columns") for W in Ws]
+    ours32 = [network_transform(W.astype(np.float64), top_percent_keep=60, project_unipartite_on="columns") for W in Ws]
+    for a, b in zip(ours32, ref_graphs):
+        assert a.dtype == np.float32 and a.shape == (c, c)
+        # same support except entries within rounding of the percentile cut; values to fp32 rounding of the fp64 product
+        differ = (a != 0) != (b != 0)
+        assert differ.mean() < 1e-5
+        keep = ~differ
+        assert np.allclose(a[keep], b[keep], rtol=2e-6, atol=2e-6 * np.abs(b).max())
+    layers = [network_transform_device(W.astype(np.float64), top_percent_keep=60, project_unipartite_on="columns")[0] for W in Ws]
+    assert all(L.n_planes == 3 and L.symmetric for L in layers)
+    dims = [2, 4, 6, 8, 10, 12]
+    emb, sigma, _, info = D.uase(layers, k, l=48, tol=1e-6, seed=42, check_dims=dims)
+    S, V, YA = port.uase_dense_fp64(ref_graphs, k)
+    assert info["converged"], info
+    assert np.allclose(sigma, S, rtol=2e-5), (sigma, S)
+    e = emb.cpu().numpy().astype(np.float64)
+    for d in dims:
+        ang = port.sin_principal_angle(port.unfolded_right_basis(YA, d), port.unfolded_right_basis(e, d))
+        assert ang <= ANGLE_TOL, (d, ang)
+    names, cd, cm = D.column_specs(dims, ["euclidean", "cosine"])
+    ours = D.distances(emb, cd, cm, N.SEQUENTIAL)[0].cpu().numpy().T
+    ref = port.rank_columns(YA, dims, ["euclidean", "cosine"], "sequential")["1"][1]
+    atol = 1e-5 * np.median(np.abs(ref), axis=0)
+    assert np.all(np.abs(ours - ref) <= SCORE_RTOL * np.abs(ref) + atol), np.max(np.abs(ours - ref) / (np.abs(ref) + atol))
