@@ -62,7 +62,7 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--n", type=int, default=0, help="override the node count (development only; named in config.workload)")
-    ap.add_argument("--block-width", type=int, default=64)
+    ap.add_argument("--block-width", type=int, default=48, help="solver block width l (default = device.default_block_width(24, n))")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer end-to-end leg (development only)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (development only)")
     return ap.parse_args()
@@ -403,7 +403,8 @@ def run_b200_arm(args):
                    "operator_applications": last["iterations"], "layer_passes": last["layer_passes"],
                    "outer_iterations": last["outer_iterations"], "converged": last["converged"],
                    "angle_bound": last["angle_bound"], "setup_s": setup_s,
-                   "solver_ms": last["total_ms"], "solver_stream_ms": last["stream_ms"], "solver_mma_ms": last["mma_ms"]},
+                   "solver_ms": last["total_ms"], "solver_stream_ms": last["stream_ms"], "solver_mma_ms": last["mma_ms"],
+                   "solver_ms_per_step": [round(i["total_ms"], 2) for i in infos]},
         "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
     }
     print(json.dumps(line), flush=True)

@@ -206,7 +206,9 @@ extern "C" int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2
     //  (B) worst <= 64 and the drop was < 2x, or (C) two filtered iterations in a row without a 30 % drop.
     double worst = 0.0;
     for (int j = 0; j < k; ++j) worst = std::max(worst, res[j] / target(j));
-    if (last_filtered) {
+    // A plain step (degree 1: the growth cap forbids a filter because lam_1 / lam_k is already large) is judged the
+    // same way when it should have gained at least 4x (its factor is lam_k / lam_l); slower plain steps are not judged.
+    if (last_filtered || (outer > 1 && predicted_gain >= 4.0)) {
       const double drop = prev_worst / std::max(worst, 1e-300);
       if (worst <= 16.0 && drop < predicted_gain / 30.0) stagnated = true;
       if (worst <= 64.0 && drop < 2.0) stagnated = true;
@@ -234,6 +236,7 @@ extern "C" int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2
       fprintf(stderr, "[uase] outer %d apps %d locked %d bound %.3e worst %.3e lam1 %.4e lamk %.4e lam_l %.4e -> degree %d\n", outer,
               stats.iterations, locked, bound, worst, lam[0], lam[k - 1], lam[l - 1], m);
     if (m <= 1) {                                            // plain subspace step: Q <- orth(M Qw)
+      predicted_gain = hi > 0.0 ? lam[k - 1] / hi : 1.0;
       RC(cholqr_pass(b.X1, b.Qn));
       RC(cholqr_pass(b.Qn, b.Q));
       continue;

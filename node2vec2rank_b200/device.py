@@ -171,6 +171,45 @@ def make_layer(x32: torch.Tensor, n_planes=None, colsum=None, check_symmetry=Tru
     return finish_layer(planes, n, ld_p, P, cs if colsum is None else colsum, check_symmetry)
 
 
+def layers_from_host(arrays, n_planes=None):
+    """float32 (n, n) host matrices (what the reference's DataLoader hands to N2V2R) -> DeviceLayers.
+
+    Double-buffered: the H2D copy of layer t+1 runs on a copy stream while the load pass (plane count, K1b
+    transform, symmetry check) of layer t runs on the current stream, so the PCIe link never waits for a kernel.
+    Pinned sources copy asynchronously; pageable ones still work (the copy then blocks the host)."""
+    dev = _dev()
+    srcs = [torch.from_numpy(np.ascontiguousarray(a)) for a in arrays]
+    if not srcs:
+        return []
+    if any(x.dtype != torch.float32 or x.shape != srcs[0].shape or x.dim() != 2 for x in srcs):
+        raise TypeError("layers_from_host expects float32 matrices of one shape")
+    cur = torch.cuda.current_stream(dev)
+    copy = torch.cuda.Stream(dev)
+    bufs = [torch.empty(srcs[0].shape, dtype=torch.float32, device=dev) for _ in range(min(2, len(srcs)))]
+    copied = [torch.cuda.Event() for _ in srcs]
+    built = [torch.cuda.Event() for _ in srcs]
+
+    def issue(t):
+        with torch.cuda.stream(copy):
+            if t >= 2:
+                copy.wait_event(built[t - 2])          # the buffer's previous layer has been consumed
+            else:
+                copy.wait_stream(cur)                  # buffers were allocated on the current stream
+            bufs[t % 2].copy_(srcs[t], non_blocking=True)
+            copied[t].record(copy)
+
+    issue(0)
+    layers = []
+    for t in range(len(srcs)):
+        if t + 1 < len(srcs):
+            issue(t + 1)
+        cur.wait_event(copied[t])
+        layers.append(make_layer(bufs[t % 2], n_planes=n_planes))
+        built[t].record(cur)
+    cur.wait_stream(copy)
+    return layers
+
+
 def finish_layer(planes, n, ld_p, P, colsum, check_symmetry=True):
     lib = N.load()
     sym = C.c_int(1)

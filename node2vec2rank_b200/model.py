@@ -20,6 +20,7 @@ import json
 import os
 import random
 import time
+import warnings
 from datetime import datetime
 
 import numpy as np
@@ -70,15 +71,22 @@ class N2V2R:
     # ---- device residency -----------------------------------------------------------------
     def _device_layers(self):
         if self._layers is None:
+            host = [None if isinstance(g, D.DeviceLayer) else np.asarray(g) for g in self.graphs]
+            arrays = [a for a in host if a is not None]
+            planes = self.config.get("storage_planes")
+            if len(arrays) > 1 and all(a.dtype == np.float32 and a.ndim == 2 and a.shape == arrays[0].shape for a in arrays):
+                built = iter(D.layers_from_host(arrays, n_planes=planes))      # H2D of layer t+1 overlaps the load pass of layer t
+                self._layers = [g if a is None else next(built) for g, a in zip(self.graphs, host)]
+                return self._layers
             layers = []
-            for g in self.graphs:
-                if isinstance(g, D.DeviceLayer):
+            for g, a in zip(self.graphs, host):
+                if a is None:
                     layers.append(g)
                 else:
-                    x = D.to_device(np.asarray(g))
+                    x = D.to_device(a)
                     if x.dtype != torch.float32:        # the reference hands fp32 to the SVD (preprocessing_utils.py:141)
                         x = x.to(torch.float32)
-                    layers.append(D.make_layer(x, n_planes=self.config.get("storage_planes")))
+                    layers.append(D.make_layer(x, n_planes=planes))
             self._layers = layers
         return self._layers
 
@@ -119,7 +127,7 @@ class N2V2R:
         self.singular_values = sigma
         self.solver_info = info
         # float64 container holding fp32-precision values, like se.UASE's YA
-        self.node_embeddings = emb.cpu().numpy().astype(np.float64)
+        self.node_embeddings = emb.double().cpu().numpy()        # widened on the device (exact)
 
     # ---- rank: replaces model.py:57-96 + model_utils.py:39-67 --------------------------------
     def __rank(self, pairwise_ranks_dict, comp_strategy):
@@ -131,7 +139,7 @@ class N2V2R:
         host = scores.cpu().numpy()
         for c in range(scores.shape[0]):
             key = str(c + 1)                                             # '1'..'T-1' or '1'..'T'
-            table = pd.DataFrame(host[c].T, index=self.node_names, columns=names)
+            table = pd.DataFrame(host[c].T, index=self.node_names, columns=names, copy=False)   # (cols, n) block, no copy
             pairwise_ranks_dict.setdefault(key, []).append(table)
 
     def fit_transform_rank(self):
@@ -174,7 +182,10 @@ class N2V2R:
             for comparison_key in keys:
                 # always rank what the (user-visible, possibly edited) table holds, like model.py:171-175
                 table = self.pairwise_ranks[comparison_key]
-                tables.append(torch.from_numpy(np.array(table.to_numpy(dtype=np.float64).T, order="C")).to(dev))
+                block = np.ascontiguousarray(table.to_numpy(dtype=np.float64).T)      # no copy for the tables __rank built
+                with warnings.catch_warnings():
+                    warnings.simplefilter("ignore")                                    # read-only view: only read for the H2D copy
+                    tables.append(torch.from_numpy(block).to(dev))
             if len({tuple(t.shape) for t in tables}) == 1:
                 bordas = D.rank_borda(torch.stack(tables))[0].cpu().numpy()          # every comparison in one launch
             else:
