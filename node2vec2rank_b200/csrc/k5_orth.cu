@@ -84,45 +84,60 @@ __device__ void jacobi_eig(double* A, double* V, int l, double* cs, int* pq, dou
     off = 0.0; tot = 0.0;
     for (int w = 0; w < (nt >> 5); ++w) { off += red[w * 2]; tot += red[w * 2 + 1]; }
     __syncthreads();
-    if (off <= 1e-30 * tot || tot == 0.0) break;
+    // converged at off(A) <= l eps ||A||_F: the roundoff floor of l(l-1) off-diagonal entries of size eps ||A|| / sqrt(l)
+    // (a tighter test is never met and costs all 40 sweeps)
+    const double lev = (double)l * 2.3e-16;
+    if (off <= lev * lev * tot || tot == 0.0) break;
     for (int r = 0; r < l - 1; ++r) {
       if (tid < half) {
         int p, q;
         if (tid == 0) { p = l - 1; q = r; }
         else { p = (r + tid) % (l - 1); q = (r - tid + (l - 1)) % (l - 1); }
-        if (p > q) { const int t = p; p = q; q = t; }
+        // no (p < q) ordering: p_i = r + i and q_i = r - i (mod l - 1) are runs of consecutive columns, which keeps the
+        // 64-bit shared-memory accesses of a warp in the block / V updates below free of bank conflicts
         const double apq = A[p * l + q], app = A[p * l + p], aqq = A[q * l + q];
         double c = 1.0, s = 0.0;
-        if (fabs(apq) > 1e-300 && fabs(apq) > 1e-18 * sqrt(fabs(app * aqq)) ) {
-          const double theta = (aqq - app) / (2.0 * apq);
-          const double t = (theta >= 0.0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
-          c = 1.0 / sqrt(t * t + 1.0);
-          s = t * c;
+        if (fabs(apq) > 1e-300 && apq * apq > 1e-36 * fabs(app * aqq)) {
+          // t = tan(angle) = b / (d + sign(d) sqrt(d^2 + b^2)), d = aqq - app, b = 2 apq (the smaller root);
+          // rsqrt / rcp sequences instead of two divisions and two square roots: this chain is the round's latency
+          const double d = aqq - app, b2 = 2.0 * apq;
+          const double x = fma(d, d, b2 * b2);
+          if (x > 1e-280 && x < 1e280) {
+            const double rr = x * rsqrt(x);
+            const double t = b2 * __drcp_rn(d + copysign(rr, d));
+            c = rsqrt(fma(t, t, 1.0));
+            s = t * c;
+          } else {                                   // out of the squared range: the division / sqrt form
+            const double theta = d / b2;
+            const double t = (theta >= 0.0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
+            c = 1.0 / sqrt(t * t + 1.0);
+            s = t * c;
+          }
         }
         cs[2 * tid] = c; cs[2 * tid + 1] = s; pq[2 * tid] = p; pq[2 * tid + 1] = q;
       }
       __syncthreads();
-      // columns: A <- A J, V <- V J
+      // A <- J^T A J one 2 x 2 block per (row pair j, column pair i): blocks are disjoint, so a single phase does both sides
+      for (int e = tid; e < half * half; e += nt) {
+        const int j = e / half, i = e - j * half;
+        const int pj = pq[2 * j], qj = pq[2 * j + 1], pi = pq[2 * i], qi = pq[2 * i + 1];
+        const double cj = cs[2 * j], sj = cs[2 * j + 1], ci = cs[2 * i], si = cs[2 * i + 1];
+        const double a00 = A[pj * l + pi], a01 = A[pj * l + qi], a10 = A[qj * l + pi], a11 = A[qj * l + qi];
+        const double b00 = ci * a00 - si * a01, b01 = si * a00 + ci * a01;       // columns
+        const double b10 = ci * a10 - si * a11, b11 = si * a10 + ci * a11;
+        A[pj * l + pi] = cj * b00 - sj * b10;                                     // rows
+        A[pj * l + qi] = cj * b01 - sj * b11;
+        A[qj * l + pi] = sj * b00 + cj * b10;
+        A[qj * l + qi] = sj * b01 + cj * b11;
+      }
+      // V <- V J
       for (int e = tid; e < l * half; e += nt) {
         const int k = e / half, i = e - k * half;
         const int p = pq[2 * i], q = pq[2 * i + 1];
         const double c = cs[2 * i], s = cs[2 * i + 1];
-        const double akp = A[k * l + p], akq = A[k * l + q];
-        A[k * l + p] = c * akp - s * akq;
-        A[k * l + q] = s * akp + c * akq;
         const double vkp = V[k * l + p], vkq = V[k * l + q];
         V[k * l + p] = c * vkp - s * vkq;
         V[k * l + q] = s * vkp + c * vkq;
-      }
-      __syncthreads();
-      // rows: A <- J^T A
-      for (int e = tid; e < l * half; e += nt) {
-        const int i = e / l, k = e - i * l;
-        const int p = pq[2 * i], q = pq[2 * i + 1];
-        const double c = cs[2 * i], s = cs[2 * i + 1];
-        const double apk = A[p * l + k], aqk = A[q * l + k];
-        A[p * l + k] = c * apk - s * aqk;
-        A[q * l + k] = s * apk + c * aqk;
       }
       __syncthreads();
     }
