@@ -213,6 +213,19 @@ size_t n2v2r_rank_workspace_bytes(int64_t n, int n_cols);
 int n2v2r_rank_borda(void* stream, const double* d_scores, int64_t n, int n_cols, int n_groups,
                      int32_t* d_positions, int64_t* d_borda, void* d_ws, size_t ws_bytes);
 
+/* ------------------------------------------------------------------------------------
+ * K12  ranking-quality read-out: binary-relevance DCG and nDCG of n_rankings rankings of
+ * `len` items each (one CTA per ranking).  Replaces relevance_and_ndcg /
+ * normalized_discounted_cumulative_gain / discounted_cumulative_gain (post_utils.py:45-122,
+ * defaults binary_relevance=True, denominator=log2(pos+2), ideal = the relevant items that
+ * occur in the ranking first) and the loop of parallel_empirical_p_ndcg (post_utils.py:125-128).
+ * d_rankings: (n_rankings x len) int32 item ids in rank order (ids outside [0, n_items) count
+ * as not relevant); d_relevant: n_items bytes (non-zero = relevant); d_ndcg: n_rankings
+ * doubles (0 when no relevant item occurs); d_dcg: n_rankings doubles or NULL.
+ * ---------------------------------------------------------------------------------- */
+int n2v2r_ndcg(void* stream, const int32_t* d_rankings, int64_t n_rankings, int64_t len,
+               const uint8_t* d_relevant, int64_t n_items, double* d_ndcg, double* d_dcg);
+
 #ifdef __cplusplus
 }
 #endif

@@ -147,6 +147,51 @@ __global__ void __launch_bounds__(1024) rank_sort_kernel(const double* __restric
   }
 }
 
+// ---- K12: binary-relevance DCG / nDCG of many rankings (post_utils.py:45-128) ------------------------
+// One CTA per ranking.  dcg = sum_pos rel[item(pos)] / log2(pos + 2); the ideal ranking puts the m relevant items
+// that occur in the ranking first: idcg = sum_{pos < m} 1 / log2(pos + 2); ndcg = dcg / idcg, 0 when m == 0
+// (post_utils.py:82-83, :113-114).  fp64, block-wide tree sums in a fixed order (deterministic).
+__global__ void __launch_bounds__(256) ndcg_kernel(const int32_t* __restrict__ rankings, int64_t n_rankings, int64_t len,
+                                                    const uint8_t* __restrict__ relevant, int64_t n_items,
+                                                    double* __restrict__ ndcg, double* __restrict__ dcg_out) {
+  __shared__ double sd[256];
+  __shared__ long long sc[256];
+  for (int64_t r = blockIdx.x; r < n_rankings; r += gridDim.x) {
+    const int32_t* row = rankings + r * len;
+    double d = 0.0;
+    long long m = 0;
+    for (int64_t pos = threadIdx.x; pos < len; pos += 256) {
+      const int32_t item = row[pos];
+      if (item >= 0 && item < n_items && relevant[item]) {
+        d += 1.0 / log2((double)(pos + 2));
+        ++m;
+      }
+    }
+    sd[threadIdx.x] = d; sc[threadIdx.x] = m;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+      if (threadIdx.x < o) { sd[threadIdx.x] += sd[threadIdx.x + o]; sc[threadIdx.x] += sc[threadIdx.x + o]; }
+      __syncthreads();
+    }
+    const double dcg = sd[0];
+    const long long mm = sc[0];
+    __syncthreads();
+    double id = 0.0;
+    for (int64_t pos = threadIdx.x; pos < mm; pos += 256) id += 1.0 / log2((double)(pos + 2));
+    sd[threadIdx.x] = id;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+      if (threadIdx.x < o) sd[threadIdx.x] += sd[threadIdx.x + o];
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+      ndcg[r] = mm > 0 ? dcg / sd[0] : 0.0;
+      if (dcg_out) dcg_out[r] = dcg;
+    }
+    __syncthreads();
+  }
+}
+
 }  // namespace n2v2r
 
 using namespace n2v2r;
@@ -202,6 +247,18 @@ extern "C" int n2v2r_rank_borda(void* stream, const double* d_scores, int64_t n,
   N2V2R_CUDA(cudaMemsetAsync(d_borda, 0, sizeof(int64_t) * n * n_groups, s));
   const int grid = n_cols < sm_count() * 2 ? n_cols : sm_count() * 2;
   rank_sort_kernel<<<grid, 1024, 0, s>>>(d_scores, n, n_cols, n_cols / n_groups, keys, idx, d_positions, (unsigned long long*)d_borda);
+  N2V2R_CHECK_LAUNCH();
+  return N2V2R_OK;
+}
+
+extern "C" int n2v2r_ndcg(void* stream, const int32_t* d_rankings, int64_t n_rankings, int64_t len,
+                          const uint8_t* d_relevant, int64_t n_items, double* d_ndcg, double* d_dcg) {
+  N2V2R_REQUIRE(d_rankings && d_relevant && d_ndcg, "ndcg: null pointer");
+  N2V2R_REQUIRE(n_rankings >= 0 && len >= 0 && n_items >= 0 && n_items < (1ll << 31), "ndcg: bad shape");
+  if (n_rankings == 0) return N2V2R_OK;
+  cudaStream_t s = (cudaStream_t)stream;
+  const int grid = (int)(n_rankings < (int64_t)sm_count() * 8 ? n_rankings : (int64_t)sm_count() * 8);
+  ndcg_kernel<<<grid, 256, 0, s>>>(d_rankings, n_rankings, len, d_relevant, n_items, d_ndcg, d_dcg);
   N2V2R_CHECK_LAUNCH();
   return N2V2R_OK;
 }

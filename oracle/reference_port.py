@@ -339,6 +339,37 @@ def stability_borda(graphs, embed_dimensions, distance_metrics, comp_strategy, s
 
 
 # --------------------------------------------------------------------------------------
+# post_utils.py (numeric part only)
+# --------------------------------------------------------------------------------------
+
+
+def discounted_cumulative_gain(relevance_vector, denominator=None):
+    """post_utils.py:45-50."""
+    rel = np.array(relevance_vector)
+    if denominator is None:
+        denominator = np.log2(np.arange(rel.shape[0]) + 2)
+    return np.sum(np.divide(2 ** rel - 1, denominator))
+
+
+def relevance_and_ndcg(ranked_items, relevant_items):
+    """post_utils.py:111-117 with the defaults of :80-108 (binary relevance: the ideal ranking has the
+    sum(relevance) relevant items first); 0 when no ranked item is relevant."""
+    relevant = set(relevant_items)
+    rel = np.array([1 if x in relevant else 0 for x in ranked_items])
+    if rel.sum() == 0:
+        return 0
+    denominator = np.log2(np.arange(len(rel)) + 2)
+    ideal = np.pad(np.ones(int(rel.sum())), (0, len(rel) - int(rel.sum())), mode="constant")
+    return discounted_cumulative_gain(rel, denominator) / np.sum(np.divide(ideal, denominator))
+
+
+def empirical_p_ndcg(ndcg, permutations, relevant_items):
+    """post_utils.py:125-128 (the joblib loop, serially)."""
+    results = [relevance_and_ndcg(p, relevant_items) for p in permutations]
+    return (np.array(results) > ndcg).sum() / len(permutations)
+
+
+# --------------------------------------------------------------------------------------
 # parity measures (SURVEY Appendix A)
 # --------------------------------------------------------------------------------------
 
