@@ -231,13 +231,21 @@ def preprocess_to_layer(x: torch.Tensor, threshold=None, top_percent_keep=100, b
     -> fp32.  The select and apply kernels share one element transform, so the cut is taken
     on exactly the values it is applied to."""
     rows, cols = x.shape
-    if rows != cols:
+    projected = rows != cols
+    if projected:
         if absolute or threshold is not None:
             x, _, _, _ = transform(x, absolute=absolute, threshold=threshold, want_f32=True)
         x = project(x, project_unipartite_on)
         absolute, threshold = False, None
-    cut = percentile_cut(x, 100 - top_percent_keep, absolute, threshold)          # runs even for keep == 100 (:134)
+    # the reference takes the percentile even for keep == 100 (:134); q = 0 is the minimum of the nonzeros, below which
+    # nothing lies, so the cut is a no-op there; for a projected layer (a Gram matrix, never all-zero unless W is) the
+    # select passes are skipped, square inputs keep them so that an all-zero graph raises like np.percentile does
+    if float(top_percent_keep) == 100.0 and projected:
+        cut = None
+    else:
+        cut = percentile_cut(x, 100 - top_percent_keep, absolute, threshold)
     n = x.shape[0]
+    check_sym = not projected            # K2 mirrors the upper triangle: W^T W is exactly symmetric, and K1b is elementwise
     if binarize:
         P = 1
     elif storage_planes:
@@ -246,12 +254,15 @@ def preprocess_to_layer(x: torch.Tensor, threshold=None, top_percent_keep=100, b
         P = 0
     if P == 0:
         # exact storage: materialise fp32 once, count the planes it needs, then split
-        out, _, _, cs = transform(x, absolute, threshold, float(cut), binarize, want_f32=True, want_colsum=True)
-        layer = make_layer(out, colsum=cs)
+        if cut is None and not binarize and not absolute and threshold is None:
+            layer = make_layer(x, check_symmetry=check_sym)          # identity transform: split the projected matrix directly
+            return layer, (x if want_f32 else None)
+        out, _, _, cs = transform(x, absolute, threshold, cut, binarize, want_f32=True, want_colsum=True)
+        layer = make_layer(out, colsum=cs, check_symmetry=check_sym)
         return layer, (out if want_f32 else None)
-    out, planes, ld_p, cs = transform(x, absolute, threshold, float(cut), binarize, want_f32=want_f32, n_planes=P,
+    out, planes, ld_p, cs = transform(x, absolute, threshold, cut, binarize, want_f32=want_f32, n_planes=P,
                                       want_colsum=True)
-    return finish_layer(planes, n, ld_p, P, cs), out
+    return finish_layer(planes, n, ld_p, P, cs, check_sym), out
 
 
 def uase(layers, k, l=64, tol=1e-5, max_iters=300, min_iters=2, seed=42, check_dims=None, algo=N.ALGO_TCGEN05,
