@@ -107,6 +107,76 @@ def test_transform_planes_colsum_and_symmetry(gpu):
     assert np.array_equal(La.planes_t[:, :, :n].float().sum(0).cpu().numpy(), a.T)
 
 
+@pytest.mark.parametrize("n", [64, 127, 200, 1000, 1284, 2049])
+def test_symmetry_and_transpose_tiles(gpu, n):
+    """64 x 64-tile kernels at sizes around the tile edges: a single asymmetric entry anywhere (corners, last partial
+    tile) must be seen, garbage in the column padding must not matter, and the transpose must match torch bit for bit."""
+    import ctypes as C
+    from node2vec2rank_b200 import _native as N
+    from node2vec2rank_b200 import device as D
+    lib = N.load()
+    rng = np.random.default_rng(n)
+    x = rng.random((n, n)).astype(np.float32)
+    x = np.where(rng.random((n, n)) < 0.3, x, 0).astype(np.float32)
+    x = np.maximum(x, x.T)
+    _, planes, ld, _ = D.transform(_t(x, gpu), n_planes=2)
+    sym = C.c_int(0)
+
+    def is_sym(p):
+        N.check(lib.n2v2r_is_symmetric(N.stream_ptr(), N.ptr(p), 2, n, ld, C.byref(sym)))
+        return bool(sym.value)
+
+    assert is_sym(planes)
+    if ld > n:                                     # padding columns are not part of the matrix
+        dirty = planes.clone()
+        dirty[:, :, n:] = 1.0
+        assert is_sym(dirty)
+    for (i, j) in [(0, n - 1), (n - 1, 0), (n // 2, n // 2 - 1), (n - 1, n - 2), (63 % n, 64 % n), (1, 0)]:
+        if i == j:
+            continue
+        bad = planes.clone()
+        bad[1, i, j] = bad[1, i, j] + 1.0           # second plane only
+        assert not is_sym(bad), (i, j)
+    a = np.triu(x) + np.tril(rng.random((n, n)).astype(np.float32), -1)
+    _, pa, ld, _ = D.transform(_t(a, gpu), n_planes=2)
+    pt = torch.full_like(pa, 7.0)
+    N.check(lib.n2v2r_transpose_planes(N.stream_ptr(), N.ptr(pa), 2, n, ld, N.ptr(pt)))
+    assert torch.equal(pt[:, :, :n], pa[:, :, :n].transpose(1, 2))
+    assert float(pt[:, :, n:].abs().sum()) == 0.0  # padding written as zeros
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_transform_fast_and_general_paths_agree(gpu, dtype):
+    """The 4-column cp.async kernel (cols % 4 == 0) against the 2-column kernel (odd leading dimension) and NumPy, for every
+    option combination, ragged row counts included."""
+    from node2vec2rank_b200 import device as D
+    rng = np.random.default_rng(3)
+    rows, cols = 1237, 2052
+    x = (rng.standard_normal((rows, cols)) * (rng.random((rows, cols)) < 0.4)).astype(dtype)
+    wide = torch.zeros((rows, cols + 1), dtype=_t(x, gpu).dtype, device=gpu)       # odd ld: general path
+    wide[:, :cols] = _t(x, gpu)
+    for absolute in (False, True):
+        for thr in (None, 0.3):
+            for cut in (None, 0.8):
+                for binarize in (False, True):
+                    y = np.abs(x) if absolute else x.copy()
+                    if thr is not None:
+                        y[y < dtype(thr)] = 0
+                    if cut is not None:
+                        y[y < dtype(cut)] = 0
+                    if binarize:
+                        y[y != 0] = 1
+                    want = y.astype(np.float32)
+                    kw = dict(absolute=absolute, threshold=thr, cut=cut, binarize=binarize)
+                    f, p, ld, cs = D.transform(_t(x, gpu), want_f32=True, n_planes=3, want_colsum=True, **kw)
+                    g, q, _, cg = D.transform(wide[:, :cols], want_f32=True, n_planes=3, want_colsum=True, **kw)
+                    assert np.array_equal(f.cpu().numpy(), want) and torch.equal(f, g)
+                    assert torch.equal(p, q) and np.array_equal(p[:, :, :cols].float().sum(0).cpu().numpy(), want)
+                    assert float(p[:, :, cols:].abs().sum()) == 0.0
+                    assert np.allclose(cs.cpu().numpy(), want.astype(np.float64).sum(0), rtol=1e-12, atol=1e-9)
+                    assert np.allclose(cg.cpu().numpy(), cs.cpu().numpy(), rtol=1e-12, atol=1e-9)
+
+
 # ---- K3/K4 ----------------------------------------------------------------------------------------
 @pytest.mark.parametrize("n,l,planes", [(1000, 64, 1), (777, 32, 3), (2048, 48, 2), (4500, 64, 1), (300, 16, 3), (1030, 80, 1)])
 def test_layer_apply_tcgen05_vs_fp64(gpu, n, l, planes):
