@@ -370,6 +370,9 @@ def rank_borda(scores: torch.Tensor, want_positions=False):
     return borda[0], (pos[0] if pos is not None else None)
 
 
+MAX_EMBED_DIM = 72        # block width l <= 80 (TMEM holds two 3l-column accumulators) minus at least 8 guard vectors
+
+
 def default_block_width(k, n):
     """Solver block width l: k plus a buffer of guard vectors, a multiple of 16 in [16, 80], < n when possible."""
     l = ((k + 24 + 15) // 16) * 16

@@ -111,6 +111,9 @@ class N2V2R:
         k = self.max_embed_dim
         if k >= n:                                      # scipy svds: "k must satisfy 0 < k < min(A.shape)"
             raise ValueError(f"`k` must be an integer satisfying `0 < k < min(A.shape)` (k={k}, n={n}).")
+        if k > D.MAX_EMBED_DIM:
+            raise NotImplementedError(f"max(embed_dimensions) = {k}: the B200 solver works on blocks of at most 80 vectors "
+                                      f"(k + >= 8 guard vectors), i.e. embedding dimensions up to {D.MAX_EMBED_DIM}")
         l = int(self.config.get("block_width") or D.default_block_width(k, n))
         T_global, offset = len(layers), 0
         sharded = bool(self.config.get("layer_sharded")) and dist.is_distributed()

@@ -68,6 +68,8 @@ class StabilityRun:
         k = m.max_embed_dim
         if k >= n:
             raise ValueError(f"`k` must be an integer satisfying `0 < k < min(A.shape)` (k={k}, n={n}).")
+        if k > D.MAX_EMBED_DIM:
+            raise NotImplementedError(f"max(embed_dimensions) = {k}: embedding dimensions up to {D.MAX_EMBED_DIM} are supported")
         if m.comp_strategy not in N.STRATEGIES:
             raise UnboundLocalError("cannot access local variable 'embed_one' where it is not associated with a value")
         l = int(cfg.get("block_width") or D.default_block_width(k, n))

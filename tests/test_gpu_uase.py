@@ -200,3 +200,27 @@ def test_c4_shaped_pipeline_vs_oracle(gpu):
     ref = port.rank_columns(YA, dims, ["euclidean", "cosine"], "sequential")["1"][1]
     atol = 1e-5 * np.median(np.abs(ref), axis=0)
     assert np.all(np.abs(ours - ref) <= SCORE_RTOL * np.abs(ref) + atol), np.max(np.abs(ours - ref) / (np.abs(ref) + atol))
+
+
+def test_wide_embedding_k64_and_limit(gpu):
+    """Embedding dimensions up to 72 run on an 80-vector block (fewer guard vectors); beyond that the mirror refuses loudly."""
+    from node2vec2rank_b200 import device as D
+    from node2vec2rank_b200.model import N2V2R
+    from node2vec2rank_b200.synthetic import block_matrices, sbm_layer_numpy
+    n, K, T, k = 1600, 70, 2, 64
+    Bs, _ = block_matrices(K, T, seed=4)
+    graphs = [sbm_layer_numpy(n, K, Bs[t], 9, t) for t in range(T)]
+    layers = [D.make_layer(torch.from_numpy(g).to(gpu)) for g in graphs]
+    assert D.default_block_width(k, n) == 80
+    emb, sigma, _, info = D.uase(layers, k, l=80, tol=1e-6, max_iters=600, seed=1, check_dims=[8, 32, k])
+    S, V, YA = port.uase_dense_fp64(graphs, k)
+    # the leading values are separated; from ~ the 40th on the spectrum is the noise bulk (relative gaps ~1e-3), where the
+    # Ritz values converge like the square of the subspace angle
+    assert np.allclose(sigma[:16], S[:16], rtol=2e-5), np.abs(sigma / S - 1)[:16].max()
+    assert np.allclose(sigma, S, rtol=2e-3), np.abs(sigma / S - 1).max()
+    e = emb.cpu().numpy().astype(np.float64)
+    G = np.einsum("tnd,tne->de", e, e)
+    assert np.allclose(np.diag(G), sigma, rtol=1e-4)
+    cfg = _cfg(None, embed_dimensions=[4, 80], verbose=-1)
+    with pytest.raises(NotImplementedError):
+        N2V2R(graphs, np.arange(n), cfg).fit_transform_rank()
