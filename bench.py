@@ -217,6 +217,8 @@ class Env:
         torch.cuda.set_device(self.local_rank)
         self.dev = N.require_gpu()
         if self.world > 1:
+            if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":      # keep stdout to the one JSON line
+                os.environ["NCCL_DEBUG"] = "WARN"
             tdist.init_process_group("nccl", device_id=self.dev)
         peaks = {}
         try:
