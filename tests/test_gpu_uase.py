@@ -1,6 +1,7 @@
 """GPU parity of the UASE solve and the end-to-end N2V2R mirror against the fp64 oracle and the
 golden vectors of the reference's own demo run (tests/golden/demo.npz)."""
 import io
+import json
 import os
 import contextlib
 
@@ -224,3 +225,41 @@ def test_wide_embedding_k64_and_limit(gpu):
     cfg = _cfg(None, embed_dimensions=[4, 80], verbose=-1)
     with pytest.raises(NotImplementedError):
         N2V2R(graphs, np.arange(n), cfg).fit_transform_rank()
+
+
+@pytest.mark.parametrize("device_resident", [False, True])
+def test_cli_from_csv_files(gpu, demo, demo_graphs, tmp_path, device_resident):
+    """node2vec2rank.py --config on adjacency CSV files (the reference's demo, rebuilt from the golden bits): DataLoader ->
+    N2V2R -> Borda -> DeDi, host float32 graphs and device-resident layers; tables compared by node name."""
+    import pandas as pd
+    from node2vec2rank_b200 import cli
+    names = [str(x) for x in demo["file_cols"]]
+    data = tmp_path / "data"
+    data.mkdir()
+    for i, g in enumerate(demo_graphs):
+        pd.DataFrame(g.astype(np.int64), index=names, columns=names).to_csv(data / f"adj_{i + 1}.csv")
+    out = tmp_path / "out"
+    out.mkdir()
+    cfg = {"data_io": {"save_dir": str(out), "data_dir": str(data), "graph_filenames": ["adj_1.csv", "adj_2.csv"],
+                       "separator": ",", "is_edge_list": False, "transpose": False},
+           "data_preprocessing": {"project_unipartite_on": None, "threshold": None, "top_percent_keep": 100, "binarize": False,
+                                  "absolute": False},
+           "fitting_ranking": {"embed_dimensions": DIMS, "distance_metrics": ["euclidean", "cosine"], "seed": 42, "verbose": 1,
+                               "comp_strategy": "sequential", "device_resident": device_resident}}
+    path = tmp_path / "config.json"
+    path.write_text(json.dumps(cfg))
+    with contextlib.redirect_stdout(io.StringIO()) as log:
+        assert cli.main(["--config", str(path)]) == 0
+    assert "Loading graphs in memory" in log.getvalue() and "Rank aggregation with Borda" in log.getvalue()
+    run_dir = out / os.listdir(out)[0]
+    assert sorted(os.listdir(run_dir)) == ["1.tsv", "1_agg.tsv", "1_degDif.tsv", "config.json"]
+    ref_nodes = [str(x) for x in demo["ref_nodes"]]
+    agg = pd.read_csv(run_dir / "1_agg.tsv", sep="\t", index_col=0)
+    agg.index = agg.index.astype(str)
+    b = agg.loc[ref_nodes, "borda_ranks"].to_numpy()
+    assert b.sum() == 22 * 1000 * 1001 // 2 and np.corrcoef(b, demo["ref_borda"])[0, 1] > 0.999
+    dd = pd.read_csv(run_dir / "1_degDif.tsv", sep="\t", index_col=0)
+    dd.index = dd.index.astype(str)
+    assert np.array_equal(dd.loc[ref_nodes, "DeDi"].to_numpy(), demo["ref_dedi"].astype(np.float64))
+    scores = pd.read_csv(run_dir / "1.tsv", sep="\t", index_col=0)
+    assert list(scores.columns) == [str(c) for c in demo["ref_columns"]] and scores.shape == (1000, 22)
