@@ -69,7 +69,7 @@ def parse_args():
 
 
 # ---- clocks ------------------------------------------------------------------------------------
-class ClockSampler:
+class SmiClockSampler:
     FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
               "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
@@ -81,9 +81,18 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
-                                          "-lms", "100"], stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+                                          "-lms", os.environ.get("N2V2R_CLOCK_MS", "200")],      # the profiling recipe's interval
+                                         stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
         except OSError:
             self.proc = None
+
+    def mark(self):
+        """Start of the timed region: samples before this line are warm-up (nvidia-smi's own start-up, which enumerates
+        every GPU of the box and can stall launches for ~0.1 s, is kept out of the timed steps by starting it early)."""
+        try:
+            self.skip = sum(1 for _ in open(self.path))
+        except OSError:
+            self.skip = 0
 
     def stop(self):
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
@@ -97,7 +106,7 @@ class ClockSampler:
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         try:
-            for line in open(self.path):
+            for line in list(open(self.path))[getattr(self, "skip", 0):]:
                 f = [x.strip() for x in line.split(",")]
                 if len(f) < 9:
                     continue
@@ -113,6 +122,74 @@ class ClockSampler:
             pass
         if sm:
             out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(mx)), reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+class ClockSampler:
+    """clocks.sm / clocks.max.sm / clocks_event_reasons of one GPU every 200 ms during the timed region (the profiling recipe's
+    nvidia-smi line, read through NVML in-process: a polling nvidia-smi process re-enumerates the box and was seen to stall
+    kernel launches for 0.1-0.3 s inside single timed steps).  Falls back to the nvidia-smi process when NVML is unavailable."""
+    REASONS = (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20), ("sw_power_cap", 0x4))
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.samples, self.skip, self.thread, self.fallback = [], 0, None, None
+        self.stop_flag = threading.Event()
+        self.period = float(os.environ.get("N2V2R_CLOCK_MS", "200")) / 1e3
+
+    def _handle(self, nv):
+        try:
+            import torch
+            pr = torch.cuda.get_device_properties(self.gpu)
+            bus = f"{pr.pci_domain_id:08X}:{pr.pci_bus_id:02X}:{pr.pci_device_id:02X}.0"
+            return nv.nvmlDeviceGetHandleByPciBusId(bus.encode())
+        except Exception:
+            return nv.nvmlDeviceGetHandleByIndex(self.gpu)
+
+    def start(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = self._handle(nv)
+            mx = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+            nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+        except Exception:
+            self.fallback = SmiClockSampler(self.gpu)
+            self.fallback.start()
+            return
+
+        def loop():
+            while not self.stop_flag.is_set():
+                try:
+                    self.samples.append((float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)), mx,
+                                         int(nv.nvmlDeviceGetCurrentClocksEventReasons(h))))
+                except Exception:
+                    pass
+                self.stop_flag.wait(self.period)
+
+        self.thread = threading.Thread(target=loop, daemon=True)
+        self.thread.start()
+
+    def mark(self):
+        if self.fallback is not None:
+            return self.fallback.mark()
+        self.skip = len(self.samples)
+
+    def stop(self):
+        if self.fallback is not None:
+            return self.fallback.stop()
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.thread is None:
+            return out
+        self.stop_flag.set()
+        self.thread.join(timeout=2)
+        got = self.samples[self.skip:] or self.samples
+        if got:
+            bits = 0
+            for _, _, r in got:
+                bits |= r
+            out.update(sm_mhz=float(np.median([g[0] for g in got])), sm_max_mhz=float(max(g[1] for g in got)),
+                       reasons=sorted(nm for nm, bit in self.REASONS if bits & bit), samples=len(got), source="nvml")
         return out
 
 
@@ -245,12 +322,14 @@ class Env:
         """W untimed steps, then exactly K steps between barrier + synchronize, CUDA events, max over ranks.
         Returns (ms per step, list of step results, clocks dict on rank 0)."""
         torch = self.torch
-        for _ in range(warmup):
-            step()
         sampler = ClockSampler(self.local_rank)
         if self.rank == 0:
             sampler.start()
+        for _ in range(warmup):
+            step()
         self.barrier()
+        if self.rank == 0:
+            sampler.mark()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         results = [step() for _ in range(steps)]
@@ -339,12 +418,14 @@ def run_b200_arm(args):
         launches = info["kernel_launches"] + 2
         return info, scores, bordas, launches
 
-    for _ in range(args.warmup):
-        step()
     sampler = ClockSampler(local_rank)
     if rank == 0:
-        sampler.start()
+        sampler.start()                  # before the warm-up: nvidia-smi's start-up stall stays out of the timed steps
+    for _ in range(args.warmup):
+        step()
     barrier()
+    if rank == 0:
+        sampler.mark()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     infos, launches = [], 0
