@@ -214,6 +214,17 @@ int n2v2r_rank_borda(void* stream, const double* d_scores, int64_t n, int n_cols
                      int32_t* d_positions, int64_t* d_borda, void* d_ws, size_t ws_bytes);
 
 /* ------------------------------------------------------------------------------------
+ * K0b  weighted edge list -> dense symmetric matrix on the device.  Replaces
+ * nx.read_weighted_edgelist + nx.to_numpy_array in DataLoader.__load_graph
+ * (dataloader.py:100-104) after the host has parsed the file and resolved duplicate
+ * edges (undirected graph: the last line of an edge wins).  d_u / d_v: endpoints as
+ * positions in the FINAL node order (negative = node not in the common node set, edge
+ * skipped); d_w: weights; d_out: zero-filled (n x ld) matrix of `dtype`.
+ * ---------------------------------------------------------------------------------- */
+int n2v2r_scatter_edges(void* stream, const int32_t* d_u, const int32_t* d_v, const double* d_w, int64_t n_edges,
+                        void* d_out, int dtype, int64_t n, int64_t ld);
+
+/* ------------------------------------------------------------------------------------
  * K12  ranking-quality read-out: binary-relevance DCG and nDCG of n_rankings rankings of
  * `len` items each (one CTA per ranking).  Replaces relevance_and_ndcg /
  * normalized_discounted_cumulative_gain / discounted_cumulative_gain (post_utils.py:45-122,

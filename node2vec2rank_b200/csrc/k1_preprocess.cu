@@ -559,6 +559,21 @@ __global__ void __launch_bounds__(256) transpose_kernel(const uint16_t* __restri
   }
 }
 
+// ---- K0b: weighted edge list (COO, duplicates already resolved) -> dense symmetric matrix --------------------------
+// out must be zero-filled; entries with an endpoint < 0 (node dropped by the node intersection) are skipped.
+template <class T>
+__global__ void __launch_bounds__(256) scatter_edges_kernel(const int32_t* __restrict__ iu, const int32_t* __restrict__ iv,
+                                                            const double* __restrict__ w, int64_t n_edges, T* __restrict__ out,
+                                                            int64_t n, int64_t ld) {
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < n_edges; e += (int64_t)gridDim.x * blockDim.x) {
+    const int32_t a = iu[e], b = iv[e];
+    if (a < 0 || b < 0 || a >= n || b >= n) continue;
+    const T v = (T)w[e];
+    out[(int64_t)a * ld + b] = v;
+    out[(int64_t)b * ld + a] = v;
+  }
+}
+
 }  // namespace n2v2r
 
 using namespace n2v2r;
@@ -683,6 +698,20 @@ extern "C" int n2v2r_transpose_planes(void* stream, const void* d_planes, int n_
   const unsigned tr = (unsigned)((n + kTile - 1) / kTile), tc = (unsigned)(ld_p / kTile);
   // blockIdx.x walks the input columns (output rows < n), blockIdx.y the input rows (output cols < ld)
   transpose_kernel<<<dim3(tr, tc, n_planes), 256, 0, s>>>((const uint16_t*)d_planes, (uint16_t*)d_out, n, ld_p);
+  N2V2R_CHECK_LAUNCH();
+  return N2V2R_OK;
+}
+
+extern "C" int n2v2r_scatter_edges(void* stream, const int32_t* d_u, const int32_t* d_v, const double* d_w, int64_t n_edges,
+                                   void* d_out, int dtype, int64_t n, int64_t ld) {
+  N2V2R_REQUIRE(d_out && n > 0 && ld >= n && n_edges >= 0, "scatter_edges: bad arguments");
+  N2V2R_REQUIRE(n_edges == 0 || (d_u && d_v && d_w), "scatter_edges: null edge arrays");
+  N2V2R_REQUIRE(dtype == N2V2R_F32 || dtype == N2V2R_F64, "scatter_edges: unknown dtype %d", dtype);
+  if (n_edges == 0) return N2V2R_OK;
+  cudaStream_t s = (cudaStream_t)stream;
+  const int grid = (int)std::min<int64_t>((n_edges + 255) / 256, (int64_t)sm_count() * 8);
+  if (dtype == N2V2R_F32) scatter_edges_kernel<float><<<grid, 256, 0, s>>>(d_u, d_v, d_w, n_edges, (float*)d_out, n, ld);
+  else scatter_edges_kernel<double><<<grid, 256, 0, s>>>(d_u, d_v, d_w, n_edges, (double*)d_out, n, ld);
   N2V2R_CHECK_LAUNCH();
   return N2V2R_OK;
 }

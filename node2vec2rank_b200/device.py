@@ -88,6 +88,18 @@ def sbm_generate(n, K, B, seed, layer, weighted=False):
     return out if ld == n else out[:, :n].contiguous()
 
 
+def dense_from_edges(iu, iv, w, n, dtype=torch.float64):
+    """K0b: (n, n) device matrix from a duplicate-free undirected weighted edge list (endpoints as final node positions,
+    negative = dropped).  Replaces nx.to_numpy_array(nx.read_weighted_edgelist(...)) (dataloader.py:100-104)."""
+    dev = _dev()
+    out = torch.zeros((n, n), dtype=dtype, device=dev)
+    u = torch.as_tensor(np.ascontiguousarray(iu, dtype=np.int32)).to(dev)
+    v = torch.as_tensor(np.ascontiguousarray(iv, dtype=np.int32)).to(dev)
+    ww = torch.as_tensor(np.ascontiguousarray(w, dtype=np.float64)).to(dev)
+    N.check(N.load().n2v2r_scatter_edges(N.stream_ptr(), N.ptr(u), N.ptr(v), N.ptr(ww), u.numel(), N.ptr(out), _dtype_code(out), n, n))
+    return out
+
+
 def select_nonzero(x: torch.Tensor, frac: float, absolute=False, threshold=None):
     """K1a: (nnz, v_lo, v_hi, virtual_index) of the nonzeros of the (abs/thresholded) matrix."""
     lib = N.load()
