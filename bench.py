@@ -482,7 +482,8 @@ def run_b200_arm(args):
         "dtype": "bf16 planes x3-split bf16 operand, fp32 accumulate (tcgen05), fp64 small dense",
         "data": "synthetic",
         "config": {"workload": w["name"], "n": n, "layers": T, "communities": K, "block_width": l, "planes_per_layer": n_planes,
-                   "layers_per_gpu": len(mine), "l2_policy": "inputs larger than L2 (each layer pass streams >= 5 GB)",
+                   "layers_per_gpu": len(mine),
+                   "l2_policy": f"inputs larger than L2 (each layer pass streams {2.0 * n * n * n_planes / 1e9:.1f} GB, L2 is 0.126 GB)",
                    "operator_applications": last["iterations"], "layer_passes": last["layer_passes"],
                    "outer_iterations": last["outer_iterations"], "converged": last["converged"],
                    "angle_bound": last["angle_bound"], "setup_s": setup_s,
