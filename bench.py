@@ -392,9 +392,14 @@ def run_b200_arm(args):
     # ---- setup (untimed): K0 generate + K1 load pass per local layer -------------------------------
     t_setup = time.perf_counter()
     layers, host_graphs = [], []
+    pre_events = []
     for t in mine:
         raw = D.sbm_generate(n, K, Bs[t], seed=GRAPH_SEED, layer=t, weighted=w["weighted"])
+        pa, pb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        pa.record()
         layer, f32 = D.preprocess_to_layer(raw, top_percent_keep=w["keep"], binarize=w["binarize"], want_f32=not args.no_e2e)
+        pb.record()
+        pre_events.append((pa, pb))
         del raw
         if f32 is not None:            # what the reference's DataLoader hands to N2V2R: float32 (n, n) on the HOST (pinned)
             h = torch.empty((n, n), dtype=torch.float32, pin_memory=True)
@@ -405,16 +410,22 @@ def run_b200_arm(args):
     torch.cuda.synchronize()
     n_planes = layers[0].n_planes if layers else 0
     setup_s = time.perf_counter() - t_setup
+    preprocess_ms = float(np.mean([a.elapsed_time(b) for a, b in pre_events][1:] or [a.elapsed_time(b) for a, b in pre_events]))
     names, cdims, cmets = D.column_specs(DIMS, METRICS)
     strategy = N.STRATEGIES[w["strategy"]]
+    rank_events = []
 
     def step():
         emb, sigma, _, info = D.uase(layers, max(DIMS), l=l, tol=1e-5, max_iters=400, seed=SOLVER_SEED, check_dims=DIMS,
                                      T_global=T, layer_offset=mine.start if len(mine) else 0)
+        ra, rb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ra.record()
         if world > 1:
             emb = ND.gather_layers(emb, T)
         scores = D.distances(emb, cdims, cmets, strategy)
         bordas = D.rank_borda(scores)[0]                       # all comparisons in one launch
+        rb.record()
+        rank_events.append((ra, rb))
         launches = info["kernel_launches"] + 2
         return info, scores, bordas, launches
 
@@ -488,7 +499,12 @@ def run_b200_arm(args):
                    "outer_iterations": last["outer_iterations"], "converged": last["converged"],
                    "angle_bound": last["angle_bound"], "setup_s": setup_s,
                    "solver_ms": last["total_ms"], "solver_stream_ms": last["stream_ms"], "solver_mma_ms": last["mma_ms"],
-                   "solver_ms_per_step": [round(i["total_ms"], 2) for i in infos]},
+                   "solver_ms_per_step": [round(i["total_ms"], 2) for i in infos],
+                   # wall-time segments: device-side load pass per layer (select + transform + planes; untimed set-up),
+                   # the solve, and the sweep (embedding gather + distances for every d + rank + Borda)
+                   "segments_ms": {"preprocess_per_layer": round(preprocess_ms, 2),
+                                   "solve": round(float(np.mean([i["total_ms"] for i in infos])), 2),
+                                   "sweep_rank_borda": round(float(np.mean([a.elapsed_time(b) for a, b in rank_events[-args.steps:]])), 2)}},
         "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
     }
     print(json.dumps(line), flush=True)
