@@ -263,3 +263,25 @@ def test_cli_from_csv_files(gpu, demo, demo_graphs, tmp_path, device_resident):
     assert np.array_equal(dd.loc[ref_nodes, "DeDi"].to_numpy(), demo["ref_dedi"].astype(np.float64))
     scores = pd.read_csv(run_dir / "1.tsv", sep="\t", index_col=0)
     assert list(scores.columns) == [str(c) for c in demo["ref_columns"]] and scores.shape == (1000, 22)
+
+
+def test_single_graph_and_strategy_errors(gpu):
+    """One graph: the reference embeds it, produces no comparison for sequential / one_vs_before (model.py:59-61) and then
+    refuses to aggregate (model.py:199); an unknown strategy fails like the reference's unbound local does."""
+    from node2vec2rank_b200.model import N2V2R
+    from node2vec2rank_b200.synthetic import block_matrices, sbm_layer_numpy
+    n, K = 400, 4
+    Bs, _ = block_matrices(K, 1, seed=1)
+    g = sbm_layer_numpy(n, K, Bs[0], 2, 0)
+    for strategy in ("sequential", "one_vs_before"):
+        m = N2V2R([g], np.arange(n), _cfg(None, embed_dimensions=[2, 4], comp_strategy=strategy, verbose=-1))
+        assert m.fit_transform_rank() == {}
+        assert m.node_embeddings.shape == (1, n, 4)
+        S, _, _ = port.uase_dense_fp64([g], 4)
+        assert np.allclose(m.singular_values, S, rtol=1e-5)
+        with pytest.raises(ValueError, match="No n2v2r embeddings found"):
+            m.aggregate_transform()
+        assert m.degree_difference_ranking() == {}
+    m = N2V2R([g, g], np.arange(n), _cfg(None, embed_dimensions=[2], comp_strategy="all_pairs", verbose=-1))
+    with pytest.raises(UnboundLocalError):
+        m.fit_transform_rank()
