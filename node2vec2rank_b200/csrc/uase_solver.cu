@@ -11,6 +11,10 @@
 //   largest unlocked Ritz value), every step deflated against the locked vectors:
 //       X_{j+1} = (2 s_{j+1}/e)(M X_j - c X_j) - s_j s_{j+1} X_{j-1}
 //   Q <- CholeskyQR2([locked | filtered])                            -- K5 + K6
+// The first filter (Ritz values of a random block: no information about outliers, so no usable growth cap) has degree
+// <= 2.  Outliers (lam_j >= 64 lam_k) are locked early, as soon as their angle estimate is below lam_k / (2 lam_j); every
+// locked column re-enters the next basis after the power step of the Rayleigh-Ritz application (M q_j / lam_j), so it
+// keeps converging at lam_l / lam_j per outer iteration while the filter works on the rest.
 // Stop: Davis-Kahan bound sqrt(sum_{j<=d} r_j^2)/(lam_d - lam_{d+1}) <= tol at every swept d, or
 // every wanted residual r_j <= max(8 eps32 lam_j, 0.02 eps32 lam_1) (the measured fp32 floor is ~eps32 lam_j),
 // or the residuals stagnate, or max_iters applications.
@@ -103,6 +107,13 @@ extern "C" int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2
   if (const char* ev = getenv("N2V2R_FLOOR_MULT")) floor_mult = atof(ev);     // developer knobs (scripts/probe_solver.py)
   if (const char* ev = getenv("N2V2R_REL_FLOOR")) rel_floor = atof(ev);
   const bool trace = getenv("N2V2R_TRACE") != nullptr;
+  // The Ritz values of the random start block say nothing about outliers (C3: lam_1 is estimated 500x too small), so the
+  // growth cap below cannot protect the first filter: its degree is limited to 2.  (N2V2R_FIRST_DEGREE: developer knob.)
+  int first_cap = 2;
+  if (const char* ev = getenv("N2V2R_FIRST_DEGREE")) first_cap = atoi(ev);
+  const bool early_lock = getenv("N2V2R_NO_EARLY_LOCK") == nullptr;
+  double need_extra = 1.0;
+  if (const char* ev = getenv("N2V2R_NEED_EXTRA")) need_extra = atof(ev);
   const double rho_max = 1e4;            // cap on T_m(x_unlocked)/T_m(x_k): keeps every fp32 column dominated by its own Ritz vector
   n2v2r_uase_stats_t stats;
   memset(&stats, 0, sizeof(stats));
@@ -197,8 +208,18 @@ extern "C" int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2
     const double floor_ = floor_mult * (double)FLT_EPSILON * std::max(lam[0], 0.0);
     auto target = [&](int j) { return std::max(floor_, rel_floor * lam[j]); };
     auto at_floor = [&](int j) { return res[j] <= target(j); };
+    // Outliers are locked early: a Ritz pair with lam_j >= 64 lam_k whose angle estimate res_j / gap_j is below
+    // lam_k / (2 lam_j) is deflated from the filter like a converged one (per filter step its leakage x_j * angle then stays
+    // below the growth of the wanted directions, which is what the growth cap needs) and keeps converging through the
+    // Rayleigh-Ritz application of every outer iteration at a factor lam_l / lam_j <= 1/64.  Convergence is still only
+    // declared on the residual targets (all_floor below).
+    auto early = [&](int j) {
+      if (!early_lock || outer < 2 || j + 1 >= l || !(lam[j] >= 64.0 * lam[k - 1]) || !(lam[k - 1] > 0.0)) return false;
+      const double gap = lam[j] - lam[j + 1];
+      return gap > 0.0 && res[j] / gap <= 0.5 * lam[k - 1] / lam[j];
+    };
     locked = 0;
-    while (locked < k && at_floor(locked)) ++locked;
+    while (locked < k && (at_floor(locked) || early(locked))) ++locked;
     bool all_floor = true;
     for (int j = 0; j < k; ++j) all_floor = all_floor && at_floor(j);
     // stagnation = the fp32 residual floor of this matrix is above the target.  After a filtered iteration:
@@ -228,9 +249,10 @@ extern "C" int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2
     if (m_cap > 1 && e > 0.0 && lam[k - 1] > hi) {
       const double xu = (lam_u - c) / e, xk = (lam[k - 1] - c) / e;
       while (m < m_cap && cheb_T(xu, m + 1) / cheb_T(xk, m + 1) <= rho_max) ++m;
-      const double need = ceil(log(4.0 * std::max(worst, 1.0)) / acosh(xk)) + 1.0;   // degree that would reach the targets
+      const double need = ceil(log(4.0 * std::max(worst, 1.0)) / acosh(xk)) + need_extra;   // degree that would reach the targets
       if (m > 1) m = std::max(2, std::min(m, (int)std::min(need, 1e6)));
       m = std::min(m, p->max_iters - stats.iterations);
+      if (outer == 1 && first_cap > 0) m = std::min(m, first_cap);
     }
     if (trace)
       fprintf(stderr, "[uase] outer %d apps %d locked %d bound %.3e worst %.3e lam1 %.4e lamk %.4e lam_l %.4e -> degree %d\n", outer,
@@ -247,6 +269,16 @@ extern "C" int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2
     const double s1 = e / (lam_u - c);
     double sg = s1;
     N2V2R_CUDA(cudaMemcpyAsync(b.X0, b.Qw, sizeof(float) * nl, cudaMemcpyDeviceToDevice, s));
+    if (locked > 0) {
+      // the locked columns leave the filter, but not the iteration: they re-enter the next basis after the power step of this
+      // Rayleigh-Ritz application, Yw_j / lam_j = M q_j / lam_j (stashed in Qn before Yw is overwritten)
+      std::vector<double> dg((size_t)l * locked, 0.0);
+      for (int j = 0; j < locked; ++j) dg[(size_t)j * locked + j] = lam[j] > 0.0 ? 1.0 / lam[j] : 1.0;
+      N2V2R_CUDA(cudaMemcpyAsync(b.C2, dg.data(), sizeof(double) * dg.size(), cudaMemcpyHostToDevice, s));
+      N2V2R_CUDA(cudaStreamSynchronize(s));          // dg is a pageable temporary
+      RC(launch_apply_small(s, b.X1, n, l, b.C2, locked, locked, b.Qn, l));
+      stats.kernel_launches += 1;
+    }
     RC(launch_axpbypcz(s, b.X1, b.X1, s1 / e, b.Qw, -c * s1 / e, nullptr, 0.0, (int64_t)nl));
     stats.kernel_launches += 2;
     float *x0 = b.X0, *x1 = b.X1, *x2 = b.X2;
@@ -261,7 +293,7 @@ extern "C" int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2
     }
     if (locked > 0) {
       RC(deflate(x1, locked));
-      N2V2R_CUDA(cudaMemcpy2DAsync(x1, sizeof(float) * l, b.Qw, sizeof(float) * l, sizeof(float) * locked, (size_t)n,
+      N2V2R_CUDA(cudaMemcpy2DAsync(x1, sizeof(float) * l, b.Qn, sizeof(float) * l, sizeof(float) * locked, (size_t)n,
                                    cudaMemcpyDeviceToDevice, s));
     }
     RC(cholqr_pass(x1, b.Qn));

@@ -86,7 +86,7 @@ def test_demo_end_to_end_vs_golden(gpu, demo, demo_graphs, tmp_path):
     assert files == ["1.tsv", "1_agg.tsv", "1_degDif.tsv", "config.json"]
 
 
-@pytest.mark.parametrize("n,K,T,weighted,l", [(1500, 6, 2, False, 48), (1200, 5, 3, True, 64)])
+@pytest.mark.parametrize("n,K,T,weighted,l", [(1500, 6, 2, False, 48), (1200, 5, 3, True, 64), (1000, 6, 5, False, 48), (900, 5, 8, True, 32)])
 def test_uase_vs_fp64_oracle_sbm(gpu, n, K, T, weighted, l):
     from node2vec2rank_b200 import device as D
     from node2vec2rank_b200.synthetic import block_matrices, sbm_layer_numpy
