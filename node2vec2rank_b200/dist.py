@@ -72,11 +72,15 @@ def gather_layers(local: torch.Tensor, T, group=None):
         raise ValueError(f"rank {rank} holds {local.shape[0]} layers, partition says {counts[rank]}")
     width = max(counts)
     n, k = local.shape[1], local.shape[2]
+    if min(counts) == width:                        # even blocks: one collective straight into the result, no padding, no cat
+        out = torch.empty((world * width, n, k), dtype=local.dtype, device=local.device)
+        torch.distributed.all_gather_into_tensor(out, local.contiguous(), group=group)
+        return out
     pad = torch.zeros((width, n, k), dtype=local.dtype, device=local.device)
     pad[:counts[rank]] = local
-    out = [torch.empty_like(pad) for _ in range(world)]
-    torch.distributed.all_gather(out, pad, group=group)
-    return torch.cat([o[:c] for o, c in zip(out, counts)], dim=0)
+    out = torch.empty((world * width, n, k), dtype=local.dtype, device=local.device)
+    torch.distributed.all_gather_into_tensor(out, pad, group=group)
+    return torch.cat([out[r * width:r * width + c] for r, c in enumerate(counts)], dim=0)
 
 
 def gather_blocks(local: torch.Tensor, total, group=None):

@@ -46,6 +46,10 @@ def _worker(rank, world, port, q):
         assert torch.equal(got, full)
         with pytest.raises(ValueError):
             ND.gather_layers(full[:0].clone() if rank == 0 else full[:3].clone(), T)
+        # even layer blocks: T = 4 over 2 ranks (single collective into the result)
+        full4 = torch.arange(4 * n * k, dtype=torch.float32).reshape(4, n, k)
+        m4 = ND.layer_partition(4, world, rank)
+        assert torch.equal(ND.gather_layers(full4[m4.start:m4.stop].clone(), 4), full4)
         # seeds of a stability run: 3 seeds over 2 ranks, score blocks (S_local, C, cols, n); a rank may hold none
         S, Cc, cols = 3, 2, 4
         sc = torch.arange(S * Cc * cols * n, dtype=torch.float64).reshape(S, Cc, cols, n)
