@@ -74,6 +74,7 @@ int n2v2r_sbm_generate(void* stream, float* d_out, int64_t n, int64_t ld, int K,
  * adjacent order statistics y_(floor(pos)) and y_(floor(pos)+1) (ascending, 0-based),
  * exactly (multi-pass radix select on the order-preserving bit pattern).  The caller does
  * the linear interpolation in the input dtype like NumPy does.  Synchronises `stream`.
+ * d_in must be contiguous (ld == cols) and 16-byte aligned (the passes read 16-byte vectors).
  * ---------------------------------------------------------------------------------- */
 size_t n2v2r_select_workspace_bytes(void);
 int n2v2r_select_nonzero(void* stream, const void* d_in, int dtype, int64_t rows, int64_t cols,
@@ -88,6 +89,8 @@ int n2v2r_select_nonzero(void* stream, const void* d_in, int dtype, int64_t rows
  * Any of d_out_f32 / d_planes / d_colsum may be NULL.  d_planes holds n_planes planes of
  * rows*ld_p bf16 each (plane stride rows*ld_p); padding columns [cols, ld_p) are zeroed.
  * d_colsum (cols doubles) must be zeroed by the caller; sums are of the fp32 output values.
+ * Fast path (4 columns per thread, cp.async ring): cols % 4 == 0, ld_in % 4 == 0 (fp32) and 16-byte
+ * aligned d_in / d_out_f32; any other layout runs the general 2-column kernel.
  * ---------------------------------------------------------------------------------- */
 int n2v2r_transform(void* stream, const void* d_in, int dtype, int64_t rows, int64_t cols, int64_t ld_in,
                     int absolute, int has_thr, double thr, int has_cut, double cut, int binarize,
@@ -99,10 +102,12 @@ int n2v2r_transform(void* stream, const void* d_in, int dtype, int64_t rows, int
  * exactly.  Synchronises `stream`. */
 int n2v2r_planes_needed(void* stream, const float* d_in, int64_t rows, int64_t cols, int64_t ld,
                         int* h_planes);
-/* 1 if the square plane set is symmetric.  Synchronises `stream`. */
+/* 1 if the square plane set is symmetric (columns >= n of the padding are ignored).  ld_p must be a
+ * multiple of 64 and d_planes 16-byte aligned.  Synchronises `stream`. */
 int n2v2r_is_symmetric(void* stream, const void* d_planes, int n_planes, int64_t n, int64_t ld_p,
                        int* h_symmetric);
-/* out = in^T for every plane (used only for non-symmetric layers). */
+/* out = in^T for every plane (used only for non-symmetric layers); padding columns of out are written as
+ * zeros.  ld_p must be a multiple of 64, both pointers 16-byte aligned. */
 int n2v2r_transpose_planes(void* stream, const void* d_planes, int n_planes, int64_t n, int64_t ld_p,
                            void* d_out);
 
