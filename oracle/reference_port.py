@@ -339,6 +339,41 @@ def stability_borda(graphs, embed_dimensions, distance_metrics, comp_strategy, s
 
 
 # --------------------------------------------------------------------------------------
+# dataloader.py (edge-list branch)
+# --------------------------------------------------------------------------------------
+
+
+def read_weighted_edgelist_dense(text, delimiter=" "):
+    """dataloader.py:100-104 restated without networkx: nx.read_weighted_edgelist(path, delimiter, nodetype=str) followed by
+    nx.to_numpy_array.  Lines are cut at '#', split on `delimiter`, need exactly (u, v, weight); the graph is undirected
+    (a later line of the same edge, in either direction, overwrites the weight); nodes are numbered in order of first
+    appearance.  Returns (node labels, dense float64 adjacency)."""
+    nodes, index, weights = [], {}, {}
+    for line in text.splitlines():
+        p = line.find("#")
+        if p >= 0:
+            line = line[:p]
+        if not line:
+            continue
+        s = line.rstrip("\n").split(delimiter)
+        if len(s) < 2:
+            continue
+        u, v, d = s[0], s[1], s[2:]
+        if len(d) != 1:
+            raise IndexError(f"Edge data {d} and data_keys (('weight', float),) are not the same length")
+        for x in (u, v):
+            if x not in index:
+                index[x] = len(nodes)
+                nodes.append(x)
+        a, b = index[u], index[v]
+        weights[(min(a, b), max(a, b))] = float(d[0])
+    A = np.zeros((len(nodes), len(nodes)), dtype=np.float64)
+    for (a, b), w in weights.items():
+        A[a, b] = A[b, a] = w
+    return nodes, A
+
+
+# --------------------------------------------------------------------------------------
 # post_utils.py (numeric part only)
 # --------------------------------------------------------------------------------------
 
