@@ -130,7 +130,7 @@ class N2V2R:
         self.singular_values = sigma
         self.solver_info = info
         # float64 container holding fp32-precision values, like se.UASE's YA
-        self.node_embeddings = emb.double().cpu().numpy()        # widened on the device (exact)
+        self.node_embeddings = D.to_host(emb.double())           # widened on the device (exact)
 
     # ---- rank: replaces model.py:57-96 + model_utils.py:39-67 --------------------------------
     def __rank(self, pairwise_ranks_dict, comp_strategy):
@@ -139,7 +139,7 @@ class N2V2R:
         names, dims, mets = D.column_specs(self.embed_dimensions, self.distance_metrics)
         strategy = N.STRATEGIES[comp_strategy]
         scores = D.distances(self._emb_dev, dims, mets, strategy)        # (C, cols, n) float64
-        host = scores.cpu().numpy()
+        host = D.to_host(scores)
         for c in range(scores.shape[0]):
             key = str(c + 1)                                             # '1'..'T-1' or '1'..'T'
             table = pd.DataFrame(host[c].T, index=self.node_names, columns=names, copy=False)   # (cols, n) block, no copy

@@ -111,7 +111,7 @@ class StabilityRun:
         union = scores.permute(1, 0, 2, 3).reshape(C, S * cols, n)
         borda = D.rank_borda(union)[0].cpu().numpy()                      # (C, n) int64
         per_seed = D.rank_borda(scores.reshape(S * C, cols, n))[0].reshape(S, C, n).cpu().numpy()
-        host = union.cpu().numpy()
+        host = D.to_host(union)
         all_names = [f"seed-{s}_{c}" for s in self.seeds for c in names]
         self.pairwise_ranks, self.pairwise_aggregate_ranks, self.per_seed_aggregate_ranks = {}, {}, {}
         for c in range(C):
