@@ -167,6 +167,59 @@ def test_full_size_c2_properties(gpu):
     assert planted[top].mean() > 0.95
 
 
+def test_full_size_c3_properties(gpu):
+    """The configuration the metric is quoted on (BASELINE configs[2]: n = 50 000, 8 weighted layers, top 10 % kept,
+    one_vs_rest) at full size, 80 GB resident.  Far beyond the CPU oracle, so the same size-independent properties as
+    for C2: singular-pair residuals recomputed with the independent SIMT product, orthogonality of the right factor,
+    Borda checksums per comparison, permutation property of the rank positions, recovery of the planted signal."""
+    from node2vec2rank_b200 import _native as N
+    from node2vec2rank_b200 import device as D
+    from node2vec2rank_b200.synthetic import block_matrices
+    if torch.cuda.get_device_properties(gpu).total_memory < 120e9:
+        pytest.skip("needs 80 GB of resident layers")
+    n, K, T, k, l = 50000, 32, 8, 24, 48
+    Bs, changed = block_matrices(K, T, seed=1)
+    layers = []
+    for t in range(T):
+        raw = D.sbm_generate(n, K, Bs[t], seed=1, layer=t, weighted=True)
+        layers.append(D.preprocess_to_layer(raw, top_percent_keep=10)[0])
+        del raw
+    assert all(L.n_planes == 2 and L.symmetric for L in layers)
+    dims = list(range(4, 25, 2))
+    emb, sigma, left, info = D.uase(layers, k, l=l, seed=42, check_dims=dims, want_left=True)
+    assert info["converged"] and info["iterations"] <= 40, info
+    assert np.all(np.diff(sigma) < 0)
+    G = torch.einsum("tnd,tne->de", emb.double(), emb.double()).cpu().numpy()
+    assert np.allclose(np.diag(G), sigma, rtol=1e-5)
+    assert np.abs(G - np.diag(np.diag(G))).max() <= 1e-5 * sigma[0]
+    U = (left.double() / torch.from_numpy(np.sqrt(sigma)).to(gpu)).float()
+    pad = torch.zeros((n, l), dtype=torch.float32, device=gpu)
+    pad[:, :k] = U
+    MU = torch.zeros_like(pad)
+    for L in layers:
+        z = D.layer_apply(L, pad, transpose=True, algo=N.ALGO_SIMT)
+        MU += D.layer_apply(L, z, transpose=False, algo=N.ALGO_SIMT)
+    lam = torch.from_numpy(sigma ** 2).to(gpu)
+    r = (MU[:, :k].double() - U.double() * lam).norm(dim=0) / lam
+    assert float(r.max()) <= 2e-5, r
+    names, cd, cm = D.column_specs(dims, ["euclidean", "cosine"])
+    scores = D.distances(emb, cd, cm, N.ONE_VS_REST)
+    assert scores.shape == (T, 22, n) and bool(torch.isfinite(scores).all())
+    borda, pos = D.rank_borda(scores, want_positions=True)
+    assert borda.shape == (T, n)
+    assert borda.sum(dim=1).tolist() == [22 * n * (n + 1) // 2] * T
+    for c in (0, T - 1):
+        assert np.array_equal(np.sort(pos[c, 21].cpu().numpy()), np.arange(n))
+    # layer t > 0 differs from every other layer in the communities whose block rows were re-drawn for it
+    b = borda.cpu().numpy()
+    for t in range(1, T):
+        planted = np.isin(np.arange(n) % K, changed[t])
+        top = np.argsort(-b[t], kind="stable")[: int(planted.sum())]
+        assert planted[top].mean() > 0.9, (t, planted[top].mean())
+    del layers, emb, left, MU, pad, scores
+    torch.cuda.empty_cache()
+
+
 def test_c4_shaped_pipeline_vs_oracle(gpu):
     """BASELINE configs[3] in miniature: bipartite layers -> W^T W (K2, tcgen05) -> cut -> planes -> UASE -> scores,
     against the oracle's network_transform (float64 np.matmul) + fp64 dense SVD.  Every cut 2..12 has a gap here."""
