@@ -120,6 +120,39 @@ def test_uase_argument_errors(gpu):
         D.uase([L], k=8, l=40)           # l not a multiple of 16
 
 
+def _degenerate_cases():
+    a = np.zeros((40, 40), np.float32)
+    a[0, 1] = a[1, 0] = 1
+    z = np.arange(512) % 3
+    B = np.array([[.9, .1, .2], [.1, .8, .3], [.2, .3, .7]], np.float32)
+    rng = np.random.default_rng(0)
+    g17 = np.triu((rng.random((17, 17)) < 0.4).astype(np.float32), 1)
+    g17 = g17 + g17.T
+    g10 = np.triu((rng.random((10, 10)) < 0.5).astype(np.float32), 1)
+    g10 = g10 + g10.T
+    return [("single-edge", [a, a], 8), ("all-zero", [np.zeros((64, 64), np.float32)] * 2, 4),
+            ("rank-3", [B[z][:, z].copy(), (B * 0.5)[z][:, z].copy()], 8), ("n17", [g17, g17.copy()], 4),
+            ("n10-block-wider-than-n", [g10, g10], 4), ("n10-k9", [g10, g10], 9)]
+
+
+@pytest.mark.parametrize("case", _degenerate_cases(), ids=lambda c: c[0])
+def test_degenerate_inputs(gpu, case):
+    """Rank-deficient, all-zero and tiny unfolded matrices: the solve ends, every output is finite and the singular values
+    (zeros included) match a dense fp64 SVD.  svds in the reference returns ~1e-7 noise for the null directions."""
+    from node2vec2rank_b200 import device as D
+    _, graphs, k = case
+    n = graphs[0].shape[0]
+    layers = [D.make_layer(torch.from_numpy(g).to(gpu)) for g in graphs]
+    emb, sigma, _, info = D.uase(layers, k, l=D.default_block_width(k, n), seed=1)
+    assert info["converged"] and info["iterations"] <= 20, info
+    e = emb.cpu().numpy()
+    assert np.isfinite(e).all() and np.isfinite(sigma).all()
+    truth = np.linalg.svd(np.hstack([g.astype(np.float64) for g in graphs]), compute_uv=False)[:k]
+    assert np.allclose(sigma, truth, rtol=1e-5, atol=1e-5 * max(truth[0], 1.0)), (sigma, truth)
+    G = np.einsum("tnd,tne->de", e.astype(np.float64), e.astype(np.float64))
+    assert np.allclose(np.diag(G), truth, rtol=1e-4, atol=1e-4 * max(truth[0], 1.0))
+
+
 def test_full_size_c2_properties(gpu):
     """BASELINE configs[1] at full size (n = 20 000, 2 binarised layers): too large for the CPU oracle, so the
     result is checked through size-independent properties: singular-pair residuals recomputed with the independent
