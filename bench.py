@@ -61,6 +61,8 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
+    ap.add_argument("--host-transfer", default="auto", choices=["auto", "dense", "packed"],
+                    help="e2e leg: how the host float32 graphs cross PCIe (device.layers_from_host)")
     ap.add_argument("--n", type=int, default=0, help="override the node count (development only; named in config.workload)")
     ap.add_argument("--block-width", type=int, default=48, help="solver block width l (default = device.default_block_width(24, n))")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer end-to-end leg (development only)")
@@ -355,6 +357,14 @@ class Env:
             self.tdist.destroy_process_group()
 
 
+def transfer_note(x):
+    """How the host graphs crossed PCIe in the e2e leg (device.layers_from_host.last_stats)."""
+    if not x or not x.get("packed_chunks"):
+        return "dense float32 copies"
+    return (f"packed on the host ({x['packed_chunks']} row chunks as bitmap + non-zero values, {x['dense_chunks']} dense), "
+            f"expanded on the device")
+
+
 def cpu_baseline_leg(w, n, T):
     n_s = min(CPU_SAMPLE_N, n)
     g = cpu_sample_graphs(w, n_s)
@@ -458,8 +468,9 @@ def run_b200_arm(args):
         del layers, scores, bordas
         torch.cuda.empty_cache()
         cfg = dict(embed_dimensions=DIMS, distance_metrics=METRICS, comp_strategy=w["strategy"], seed=SOLVER_SEED,
-                   save_dir=None, verbose=-1, block_width=l, layer_sharded=world > 1)
+                   save_dir=None, verbose=-1, block_width=l, layer_sharded=world > 1, host_transfer=args.host_transfer)
         node_names = np.arange(n)
+        xfer = {}
 
         def e2e_step():
             m = N2V2R(graphs=host_graphs, nodes=node_names, config=cfg)
@@ -467,6 +478,7 @@ def run_b200_arm(args):
             agg = m.aggregate_transform()               # rank + Borda + D2H
             d2h = m.node_embeddings.shape[0] * n * max(DIMS) * 4 + sum(v.shape[0] * v.shape[1] * 8 for v in ranks.values()) \
                 + sum(v.shape[0] * 8 for v in agg.values())
+            xfer.update(m.transfer_stats or {})
             return d2h
 
         for _ in range(args.warmup):
@@ -478,7 +490,11 @@ def run_b200_arm(args):
             d2h = e2e_step()
         barrier()
         e2e_s = reduce_max((time.perf_counter() - t0) / max(args.steps, 1))
-        e2e = {"value": e2e_s, "unit": "s", "h2d_bytes_per_step": int(T) * n * n * 4, "d2h_bytes_per_step": int(d2h),
+        # whole job: this rank's bytes scaled from its layers to all T (the layers have the same density)
+        e2e = {"value": e2e_s, "unit": "s",
+               "h2d_bytes_per_step": int(xfer.get("h2d_bytes", len(mine) * n * n * 4) * T / max(len(mine), 1)),
+               "d2h_bytes_per_step": int(d2h), "host_graph_bytes_per_step": int(T) * n * n * 4,
+               "host_transfer": transfer_note(xfer),
                "api": "N2V2R(graphs=float32 host arrays).fit_transform_rank() + aggregate_transform()"}
 
     if rank != 0:
@@ -583,16 +599,19 @@ def run_b200_c5(args, w):
         del layers
         torch.cuda.empty_cache()
         cfg = dict(embed_dimensions=DIMS, distance_metrics=METRICS, comp_strategy=w["strategy"], seed=None, save_dir=None,
-                   verbose=-1, block_width=l, seed_sharded=env.world > 1)
+                   verbose=-1, block_width=l, seed_sharded=env.world > 1, host_transfer=args.host_transfer)
+        xfer = {}
 
         def e2e_step():
             run = StabilityRun(graphs=host_graphs, nodes=np.arange(n), config=cfg, seeds=seeds)
             agg = run.run()                       # H2D of the graphs, plane build, all solves, Borda across runs, D2H of the tables
+            xfer.update(run._model.transfer_stats or {})
             return sum(v.shape[0] * v.shape[1] * 8 for v in run.pairwise_ranks.values()) + sum(v.shape[0] * 8 for v in agg.values()) \
                 + sum(v.shape[0] * v.shape[1] * 8 for v in run.per_seed_aggregate_ranks.values())
 
         e2e_s, d2h = env.timed_host(e2e_step, args.steps, min(args.warmup, 1))
-        e2e = {"value": e2e_s, "unit": "s", "h2d_bytes_per_step": int(T) * n * n * 4, "d2h_bytes_per_step": int(d2h),
+        e2e = {"value": e2e_s, "unit": "s", "h2d_bytes_per_step": int(xfer.get("h2d_bytes", int(T) * n * n * 4)),
+               "d2h_bytes_per_step": int(d2h), "host_graph_bytes_per_step": int(T) * n * n * 4, "host_transfer": transfer_note(xfer),
                "api": "StabilityRun(graphs=float32 host arrays, seeds).run()"}
     if env.rank != 0:
         env.finish()

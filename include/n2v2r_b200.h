@@ -230,6 +230,25 @@ int n2v2r_scatter_edges(void* stream, const int32_t* d_u, const int32_t* d_v, co
                         void* d_out, int dtype, int64_t n, int64_t ld);
 
 /* ------------------------------------------------------------------------------------
+ * K0c  sparse host->device transfer of a dense fp32 layer.  The reference converts every
+ * dense float32 graph to CSC on the host before the SVD (N2V2R.__fit, model.py:51-55); here
+ * the host side of that conversion only serves the PCIe copy: n2v2r_host_pack_nonzeros
+ * (HOST code, `threads` std::threads, no CUDA call) writes a bitmap (one bit per entry,
+ * ceil(cols/32) 32-bit words per row, bit j of word w = entry 32 w + j) and the non-zero
+ * entries of each row in column order; h_row_start[r] is the position of row r's first
+ * value in h_values (rows are claimed by the threads in blocks, so the positions are not
+ * monotone in r).  "Zero" means all 32 bits zero, so the round trip is bit-exact.
+ * *nnz = number of values written, or -1 when they do not fit `capacity` (the caller then
+ * copies the layer dense).  n2v2r_unpack_nonzeros rebuilds the dense (rows x ld) fp32
+ * matrix on the device from device copies of the three arrays (columns cols..ld-1 are not
+ * written).
+ * ---------------------------------------------------------------------------------- */
+int n2v2r_host_pack_nonzeros(const void* h_a, int64_t rows, int64_t cols, int64_t ld, uint32_t* h_bitmap,
+                             void* h_values, int64_t capacity, int64_t* h_row_start, int threads, int64_t* nnz);
+int n2v2r_unpack_nonzeros(void* stream, const uint32_t* d_bitmap, const void* d_values, const int64_t* d_row_start,
+                          int64_t rows, int64_t cols, void* d_out, int64_t ld);
+
+/* ------------------------------------------------------------------------------------
  * K12  ranking-quality read-out: binary-relevance DCG and nDCG of n_rankings rankings of
  * `len` items each (one CTA per ranking).  Replaces relevance_and_ndcg /
  * normalized_discounted_cumulative_gain / discounted_cumulative_gain (post_utils.py:45-122,

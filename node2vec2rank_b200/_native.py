@@ -76,6 +76,8 @@ SIGNATURES = {
     "n2v2r_rank_borda": (_i, [_vp, _vp, _i64, _i, _i, _vp, _vp, _vp, _sz]),
     "n2v2r_ndcg": (_i, [_vp, _vp, _i64, _i64, _vp, _i64, _vp, _vp]),
     "n2v2r_scatter_edges": (_i, [_vp, _vp, _vp, _vp, _i64, _vp, _i, _i64, _i64]),
+    "n2v2r_host_pack_nonzeros": (_i, [_vp, _i64, _i64, _i64, _vp, _vp, _i64, _vp, _i, _vp]),
+    "n2v2r_unpack_nonzeros": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _vp, _i64]),
 }
 
 _lib = None

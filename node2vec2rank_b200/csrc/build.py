@@ -19,7 +19,9 @@ PKG = os.path.dirname(HERE)
 ROOT = os.path.dirname(PKG)
 OUT = os.path.join(PKG, "libn2v2r_b200.so")
 OBJ = os.path.join(ROOT, "build", "obj")
-SOURCES = ["api.cu", "k1_preprocess.cu", "k3_stream.cu", "k3_tcgen05.cu", "k5_orth.cu", "k9_rank.cu", "uase_solver.cu"]
+SOURCES = ["api.cu", "k0_pack.cu", "k1_preprocess.cu", "k3_stream.cu", "k3_tcgen05.cu", "k5_orth.cu", "k9_rank.cu", "uase_solver.cu"]
+HOST_SOURCES = ["host_pack.cpp"]          # plain C++ (g++): host-side packing for the sparse PCIe transfer
+HOST_FLAGS = ["-O3", "-std=c++17", "-fPIC", "-pthread", "-fvisibility=default"]
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
          "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default"]
 
@@ -33,11 +35,11 @@ def nvcc():
 
 def _digest():
     h = hashlib.sha256()
-    names = sorted(f for f in os.listdir(HERE) if f.endswith((".cu", ".cuh")))
+    names = sorted(f for f in os.listdir(HERE) if f.endswith((".cu", ".cuh", ".cpp")))
     for f in names + [os.path.join(ROOT, "include", "n2v2r_b200.h")]:
         with open(os.path.join(HERE, f) if not os.path.isabs(f) else f, "rb") as fh:
             h.update(fh.read())
-    h.update(" ".join(FLAGS).encode())
+    h.update(" ".join(FLAGS + HOST_FLAGS).encode())
     return h.hexdigest()
 
 
@@ -57,9 +59,17 @@ def build(force: bool = False, verbose: bool = True) -> str:
             raise RuntimeError(f"nvcc failed on {src}:\n{r.stdout}\n{r.stderr}")
         return obj
 
+    def host_one(src):
+        obj = os.path.join(OBJ, src.replace(".cpp", ".o"))
+        cxx = shutil.which("g++") or "g++"
+        r = subprocess.run([cxx, *HOST_FLAGS, "-c", os.path.join(HERE, src), "-o", obj], capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(f"g++ failed on {src}:\n{r.stdout}\n{r.stderr}")
+        return obj
+
     with concurrent.futures.ThreadPoolExecutor(max_workers=min(8, len(SOURCES))) as ex:
-        objs = list(ex.map(one, SOURCES))
-    cmd = [exe, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", OUT, *objs]
+        objs = list(ex.map(one, SOURCES)) + [host_one(s) for s in HOST_SOURCES]
+    cmd = [exe, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-Xcompiler", "-pthread", "-o", OUT, *objs]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")

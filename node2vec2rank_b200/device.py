@@ -6,6 +6,7 @@ falls back to the CPU.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from dataclasses import dataclass, field
 
 import numpy as np
@@ -196,18 +197,149 @@ def make_layer(x32: torch.Tensor, n_planes=None, colsum=None, check_symmetry=Tru
     return finish_layer(planes, n, ld_p, P, cs if colsum is None else colsum, check_symmetry)
 
 
-def layers_from_host(arrays, n_planes=None):
+PACK_MIN_ENTRIES = 4_000_000          # below this a layer crosses PCIe dense (the packed pipeline has fixed costs)
+PACK_CHUNK_ENTRIES = 300_000_000      # rows are packed and copied in chunks of about this many entries
+PACK_MAX_DENSITY = 0.125              # staging capacity for the non-zero values, as a fraction of a chunk's entries
+_pack_staging = {}                    # (chunk_rows, cols) -> two pinned staging slots, kept across calls (pinning is slow)
+
+
+def host_threads():
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
+def _staging(chunk_rows, cols):
+    words = (cols + 31) // 32
+    cap = max(8, int(chunk_rows * cols * PACK_MAX_DENSITY))
+    key = (chunk_rows, cols, cap)
+    if key not in _pack_staging:
+        _pack_staging.clear()                                      # one shape at a time stays pinned
+        _pack_staging[key] = [dict(bitmap=torch.empty((chunk_rows, words), dtype=torch.int32, pin_memory=True),
+                                   values=torch.empty(cap, dtype=torch.float32, pin_memory=True),
+                                   row_start=torch.empty(chunk_rows, dtype=torch.int64, pin_memory=True)) for _ in range(2)]
+    return _pack_staging[key]
+
+
+def layers_from_host(arrays, n_planes=None, transfer="auto"):
     """float32 (n, n) host matrices (what the reference's DataLoader hands to N2V2R) -> DeviceLayers.
 
-    Double-buffered: the H2D copy of layer t+1 runs on a copy stream while the load pass (plane count, K1b
-    transform, symmetry check) of layer t runs on the current stream, so the PCIe link never waits for a kernel.
-    Pinned sources copy asynchronously; pageable ones still work (the copy then blocks the host)."""
-    dev = _dev()
+    transfer = "dense": double-buffered H2D of the dense matrices (the copy of layer t+1 runs on a copy stream while
+    the load pass of layer t runs on the current stream).  Pinned sources copy asynchronously; pageable ones block.
+    transfer = "packed": the layers cross PCIe as bitmap + non-zero values (K0c): a producer thread packs chunks of
+    rows with every host core (n2v2r_host_pack_nonzeros), copies them and expands them on the copy stream into one of
+    two dense device buffers while the current stream runs the load pass of the previous layer.  The reference does
+    the same dense -> sparse conversion on the host (csc_matrix, model.py:51-53).  A chunk denser than
+    PACK_MAX_DENSITY is copied dense, and so is everything after it.
+    transfer = "auto": packed for layers of at least PACK_MIN_ENTRIES entries, dense below."""
     srcs = [torch.from_numpy(np.ascontiguousarray(a)) for a in arrays]
     if not srcs:
         return []
     if any(x.dtype != torch.float32 or x.shape != srcs[0].shape or x.dim() != 2 for x in srcs):
         raise TypeError("layers_from_host expects float32 matrices of one shape")
+    if transfer not in ("auto", "dense", "packed"):
+        raise ValueError(f"unknown transfer mode {transfer!r}")
+    if transfer == "auto":
+        transfer = "packed" if srcs[0].numel() >= PACK_MIN_ENTRIES else "dense"
+    if transfer == "packed":
+        return _layers_from_host_packed(srcs, n_planes)
+    return _layers_from_host_dense(srcs, n_planes)
+
+
+def _layers_from_host_packed(srcs, n_planes):
+    import queue
+    import threading
+    dev = _dev()
+    lib = N.load()
+    rows, cols = srcs[0].shape
+    words = (cols + 31) // 32
+    chunk_rows = max(1, min(rows, PACK_CHUNK_ENTRIES // max(cols, 1)))
+    slots = _staging(chunk_rows, cols)
+    cur = torch.cuda.current_stream(dev)
+    copy = torch.cuda.Stream(dev)
+    dense = [torch.empty((rows, cols), dtype=torch.float32, device=dev) for _ in range(min(2, len(srcs)))]
+    twins = [{k: torch.empty_like(v, device=dev) for k, v in slot.items()} for slot in slots]
+    copy.wait_stream(cur)                                 # the buffers were allocated on the current stream
+    ready, consumed = queue.Queue(), queue.Queue()
+    threads = host_threads()
+    stats = dict(packed_chunks=0, dense_chunks=0, h2d_bytes=0)
+
+    def produce():
+        try:
+            torch.cuda.set_device(dev)
+            sent = []                                     # per chunk: event after its H2D (the staging slot is free again)
+            dense_mode = False
+            with torch.cuda.stream(copy):
+                for t, src in enumerate(srcs):
+                    if t >= 2:
+                        done = consumed.get()             # the load pass of layer t-2 has read this dense buffer
+                        if done is None:                  # the consumer failed
+                            return
+                        copy.wait_event(done)
+                    out = dense[t % 2]
+                    for r0 in range(0, rows, chunk_rows):
+                        r1 = min(rows, r0 + chunk_rows)
+                        nnz = C.c_int64(-1)
+                        if not dense_mode:
+                            c = len(sent)
+                            slot, twin = slots[c % 2], twins[c % 2]
+                            if c >= 2:
+                                sent[c - 2].synchronize()
+                            N.check(lib.n2v2r_host_pack_nonzeros(C.c_void_p(src[r0:r1].data_ptr()), r1 - r0, cols, cols,
+                                                                 N.ptr(slot["bitmap"]), N.ptr(slot["values"]),
+                                                                 slot["values"].numel() - 8, N.ptr(slot["row_start"]),
+                                                                 threads, C.byref(nnz)))
+                        if nnz.value < 0:                 # too dense (or dense mode): this chunk crosses PCIe as it is
+                            dense_mode = True
+                            out[r0:r1].copy_(src[r0:r1], non_blocking=True)
+                            stats["dense_chunks"] += 1
+                            stats["h2d_bytes"] += (r1 - r0) * cols * 4
+                            continue
+                        k = nnz.value
+                        twin["bitmap"][: r1 - r0].copy_(slot["bitmap"][: r1 - r0], non_blocking=True)
+                        twin["row_start"][: r1 - r0].copy_(slot["row_start"][: r1 - r0], non_blocking=True)
+                        twin["values"][:k].copy_(slot["values"][:k], non_blocking=True)
+                        ev = torch.cuda.Event()
+                        ev.record(copy)
+                        sent.append(ev)
+                        N.check(lib.n2v2r_unpack_nonzeros(C.c_void_p(copy.cuda_stream), N.ptr(twin["bitmap"]), N.ptr(twin["values"]),
+                                                          N.ptr(twin["row_start"]), r1 - r0, cols, N.ptr(out[r0:r1]), cols))
+                        stats["packed_chunks"] += 1
+                        stats["h2d_bytes"] += (r1 - r0) * (words * 4 + 8) + k * 4
+                    ev = torch.cuda.Event()
+                    ev.record(copy)
+                    ready.put(ev)
+        except BaseException as ex:  # noqa: BLE001  (handed to the consumer)
+            ready.put(ex)
+
+    worker = threading.Thread(target=produce, name="n2v2r-pack", daemon=True)
+    worker.start()
+    layers = []
+    try:
+        for t in range(len(srcs)):
+            ev = ready.get()
+            if isinstance(ev, BaseException):
+                raise ev
+            cur.wait_event(ev)
+            layers.append(make_layer(dense[t % 2], n_planes=n_planes))
+            done = torch.cuda.Event()
+            done.record(cur)
+            consumed.put(done)
+    except BaseException:
+        consumed.put(None)
+        consumed.put(None)
+        raise
+    finally:
+        worker.join()
+    cur.wait_stream(copy)
+    layers_from_host.last_stats = stats
+    return layers
+
+
+def _layers_from_host_dense(srcs, n_planes):
+    dev = _dev()
+    layers_from_host.last_stats = dict(packed_chunks=0, dense_chunks=len(srcs), h2d_bytes=sum(x.numel() * 4 for x in srcs))
     cur = torch.cuda.current_stream(dev)
     copy = torch.cuda.Stream(dev)
     bufs = [torch.empty(srcs[0].shape, dtype=torch.float32, device=dev) for _ in range(min(2, len(srcs)))]

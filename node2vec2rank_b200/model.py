@@ -54,6 +54,7 @@ class N2V2R:
         self.singular_values = None
         self.solver_info = None
         self._layers = None            # device-resident layers (built lazily, reused by DeDi)
+        self.transfer_stats = None     # how the host graphs crossed PCIe (device.layers_from_host.last_stats)
         self._emb_dev = None
 
         if self.config["seed"]:        # falsy seed (None or 0) => unseeded, model.py:36
@@ -74,8 +75,10 @@ class N2V2R:
             host = [None if isinstance(g, D.DeviceLayer) else np.asarray(g) for g in self.graphs]
             arrays = [a for a in host if a is not None]
             planes = self.config.get("storage_planes")
-            if len(arrays) > 1 and all(a.dtype == np.float32 and a.ndim == 2 and a.shape == arrays[0].shape for a in arrays):
-                built = iter(D.layers_from_host(arrays, n_planes=planes))      # H2D of layer t+1 overlaps the load pass of layer t
+            if arrays and all(a.dtype == np.float32 and a.ndim == 2 and a.shape == arrays[0].shape for a in arrays):
+                # H2D of layer t+1 overlaps the load pass of layer t; large sparse layers cross PCIe packed (K0c)
+                built = iter(D.layers_from_host(arrays, n_planes=planes, transfer=self.config.get("host_transfer", "auto")))
+                self.transfer_stats = D.layers_from_host.last_stats
                 self._layers = [g if a is None else next(built) for g, a in zip(self.graphs, host)]
                 return self._layers
             layers = []
