@@ -361,7 +361,8 @@ def transfer_note(x):
     """How the host graphs crossed PCIe in the e2e leg (device.layers_from_host.last_stats)."""
     if not x or not x.get("packed_chunks"):
         return "dense float32 copies"
-    return (f"packed on the host ({x['packed_chunks']} row chunks as bitmap + non-zero values, {x['dense_chunks']} dense), "
+    return (f"packed on the host ({x['packed_chunks']} row chunks as bitmap + non-zero values, {x['dense_chunks']} dense; "
+            f"{x.get('threads', 0)} host threads, {x.get('pack_s', 0):.3f} s packing of {x.get('total_s', 0):.3f} s transfer + load pass), "
             f"expanded on the device")
 
 
@@ -472,10 +473,17 @@ def run_b200_arm(args):
         node_names = np.arange(n)
         xfer = {}
 
+        phases = []
+
         def e2e_step():
+            ta = time.perf_counter()
             m = N2V2R(graphs=host_graphs, nodes=node_names, config=cfg)
             ranks = m.fit_transform_rank()              # H2D of the graphs + plane build + solve + distances + D2H of the tables
+            tb = time.perf_counter()
             agg = m.aggregate_transform()               # rank + Borda + D2H
+            phases.append({"fit_transform_rank_s": round(tb - ta, 4), "aggregate_s": round(time.perf_counter() - tb, 4),
+                           "transfer_and_load_s": round((m.transfer_stats or {}).get("total_s", 0.0), 4),
+                           "solver_s": round(m.solver_info["total_ms"] / 1e3, 4)})
             d2h = m.node_embeddings.shape[0] * n * max(DIMS) * 4 + sum(v.shape[0] * v.shape[1] * 8 for v in ranks.values()) \
                 + sum(v.shape[0] * 8 for v in agg.values())
             xfer.update(m.transfer_stats or {})
@@ -494,7 +502,7 @@ def run_b200_arm(args):
         e2e = {"value": e2e_s, "unit": "s",
                "h2d_bytes_per_step": int(xfer.get("h2d_bytes", len(mine) * n * n * 4) * T / max(len(mine), 1)),
                "d2h_bytes_per_step": int(d2h), "host_graph_bytes_per_step": int(T) * n * n * 4,
-               "host_transfer": transfer_note(xfer),
+               "host_transfer": transfer_note(xfer), "phases_per_step": phases[-args.steps:],
                "api": "N2V2R(graphs=float32 host arrays).fit_transform_rank() + aggregate_transform()"}
 
     if rank != 0:

@@ -9,6 +9,7 @@
 //
 // Plain C++ (g++): no CUDA in this file.
 #include <stdint.h>
+#include <stdlib.h>
 #include <string.h>
 #include <atomic>
 #include <thread>
@@ -23,6 +24,7 @@ void set_error(const char* fmt, ...);
 namespace {
 
 constexpr int64_t kRowsPerClaim = 4;
+constexpr int64_t kPrefetchAhead = 2048;      // software prefetch distance in entries (8 KB); N2V2R_PACK_PREFETCH overrides
 
 // 32 consecutive entries -> bit j set when entry j is non-zero (any bit set)
 inline uint32_t mask32_scalar(const uint32_t* p, int count) {
@@ -51,12 +53,14 @@ const CompactLut& compact_lut() {
 // one row: bitmap words + compacted values (branch-free: 8 entries per step, permute the non-zeros to the front, store
 // all 8 lanes and advance by the popcount -- `vals` needs 8 entries of slack); returns the number of non-zeros
 __attribute__((target("avx2,popcnt"))) int64_t pack_row_avx2(const uint32_t* row, int64_t cols, uint32_t* bits, uint32_t* vals,
-                                                              const CompactLut& lut) {
+                                                              const CompactLut& lut, int64_t ahead) {
   const int64_t full = cols / 32;
   const __m256i z = _mm256_setzero_si256();
   int64_t k = 0;
   for (int64_t w = 0; w < full; ++w) {
     const uint32_t* p = row + 32 * w;
+    _mm_prefetch((const char*)(p + ahead), _MM_HINT_T0);          // two lines per word, a few KB ahead:
+    _mm_prefetch((const char*)(p + ahead + 16), _MM_HINT_T0);     // more misses in flight per core
     uint32_t word = 0;
 #pragma GCC unroll 4
     for (int q = 0; q < 4; ++q) {
@@ -110,6 +114,8 @@ extern "C" int n2v2r_host_pack_nonzeros(const void* h_a, int64_t rows, int64_t c
   if (rows == 0 || cols == 0) return N2V2R_OK;
   const bool avx2 = __builtin_cpu_supports("avx2") && __builtin_cpu_supports("popcnt");
   const CompactLut& lut = compact_lut();
+  const char* env = getenv("N2V2R_PACK_PREFETCH");
+  const int64_t ahead = env ? atoll(env) : kPrefetchAhead;
   const int64_t words = (cols + 31) / 32;
   const uint32_t* a = (const uint32_t*)h_a;
   uint32_t* values = (uint32_t*)h_values;
@@ -131,7 +137,7 @@ extern "C" int n2v2r_host_pack_nonzeros(const void* h_a, int64_t rows, int64_t c
       const int64_t r1 = r0 + kRowsPerClaim < rows ? r0 + kRowsPerClaim : rows;
       int64_t k = 0;
       for (int64_t r = r0; r < r1; ++r) {
-        const int64_t got = avx2 ? pack_row_avx2(a + r * ld, cols, h_bitmap + r * words, tmp.data() + k, lut)
+        const int64_t got = avx2 ? pack_row_avx2(a + r * ld, cols, h_bitmap + r * words, tmp.data() + k, lut, ahead)
                                  : pack_row_plain(a + r * ld, cols, h_bitmap + r * words, tmp.data() + k);
         counts[r - r0] = got;
         k += got;

@@ -7,6 +7,7 @@ from __future__ import annotations
 
 import ctypes as C
 import os
+import time
 from dataclasses import dataclass, field
 
 import numpy as np
@@ -199,7 +200,7 @@ def make_layer(x32: torch.Tensor, n_planes=None, colsum=None, check_symmetry=Tru
 
 PACK_MIN_ENTRIES = 4_000_000          # below this a layer crosses PCIe dense (the packed pipeline has fixed costs)
 PACK_CHUNK_ENTRIES = 300_000_000      # rows are packed and copied in chunks of about this many entries
-PACK_MAX_DENSITY = 0.125              # staging capacity for the non-zero values, as a fraction of a chunk's entries
+PACK_MAX_DENSITY = 0.3                # staging capacity for the non-zero values, as a fraction of a chunk's entries
 _pack_staging = {}                    # (chunk_rows, cols) -> two pinned staging slots, kept across calls (pinning is slow)
 
 
@@ -263,7 +264,8 @@ def _layers_from_host_packed(srcs, n_planes):
     copy.wait_stream(cur)                                 # the buffers were allocated on the current stream
     ready, consumed = queue.Queue(), queue.Queue()
     threads = host_threads()
-    stats = dict(packed_chunks=0, dense_chunks=0, h2d_bytes=0)
+    stats = dict(packed_chunks=0, dense_chunks=0, h2d_bytes=0, pack_s=0.0, producer_s=0.0, total_s=0.0, threads=threads)
+    t_begin = time.perf_counter()
 
     def produce():
         try:
@@ -286,10 +288,12 @@ def _layers_from_host_packed(srcs, n_planes):
                             slot, twin = slots[c % 2], twins[c % 2]
                             if c >= 2:
                                 sent[c - 2].synchronize()
+                            t_pack = time.perf_counter()
                             N.check(lib.n2v2r_host_pack_nonzeros(C.c_void_p(src[r0:r1].data_ptr()), r1 - r0, cols, cols,
                                                                  N.ptr(slot["bitmap"]), N.ptr(slot["values"]),
                                                                  slot["values"].numel() - 8, N.ptr(slot["row_start"]),
                                                                  threads, C.byref(nnz)))
+                            stats["pack_s"] += time.perf_counter() - t_pack
                         if nnz.value < 0:                 # too dense (or dense mode): this chunk crosses PCIe as it is
                             dense_mode = True
                             out[r0:r1].copy_(src[r0:r1], non_blocking=True)
@@ -310,6 +314,7 @@ def _layers_from_host_packed(srcs, n_planes):
                     ev = torch.cuda.Event()
                     ev.record(copy)
                     ready.put(ev)
+            stats["producer_s"] = time.perf_counter() - t_begin
         except BaseException as ex:  # noqa: BLE001  (handed to the consumer)
             ready.put(ex)
 
@@ -333,13 +338,16 @@ def _layers_from_host_packed(srcs, n_planes):
     finally:
         worker.join()
     cur.wait_stream(copy)
+    stats["total_s"] = time.perf_counter() - t_begin
     layers_from_host.last_stats = stats
     return layers
 
 
 def _layers_from_host_dense(srcs, n_planes):
     dev = _dev()
-    layers_from_host.last_stats = dict(packed_chunks=0, dense_chunks=len(srcs), h2d_bytes=sum(x.numel() * 4 for x in srcs))
+    t_begin = time.perf_counter()
+    stats = dict(packed_chunks=0, dense_chunks=len(srcs), h2d_bytes=sum(x.numel() * 4 for x in srcs), total_s=0.0)
+    layers_from_host.last_stats = stats
     cur = torch.cuda.current_stream(dev)
     copy = torch.cuda.Stream(dev)
     bufs = [torch.empty(srcs[0].shape, dtype=torch.float32, device=dev) for _ in range(min(2, len(srcs)))]
@@ -364,6 +372,7 @@ def _layers_from_host_dense(srcs, n_planes):
         layers.append(make_layer(bufs[t % 2], n_planes=n_planes))
         built[t].record(cur)
     cur.wait_stream(copy)
+    stats["total_s"] = time.perf_counter() - t_begin        # host time: the last load pass may still be running
     return layers
 
 
