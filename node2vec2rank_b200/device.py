@@ -205,10 +205,16 @@ _pack_staging = {}                    # (chunk_rows, cols) -> two pinned staging
 
 
 def host_threads():
+    """Host threads for the packing: the cores this process may use, shared between the ranks of one node."""
     try:
-        return max(1, len(os.sched_getaffinity(0)))
+        cores = len(os.sched_getaffinity(0))
     except AttributeError:
-        return max(1, os.cpu_count() or 1)
+        cores = os.cpu_count() or 1
+    try:
+        local_world = max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1")))
+    except ValueError:
+        local_world = 1
+    return max(1, cores // local_world)
 
 
 def _staging(chunk_rows, cols):
