@@ -66,3 +66,14 @@ def test_pack_overflow_and_arguments():
     n = C.c_int64(0)
     assert lib.n2v2r_host_pack_nonzeros(None, 4, 4, 4, None, None, 4, None, 1, C.byref(n)) == 1      # N2V2R_EINVAL
     assert b"bad argument" in lib.n2v2r_last_error()
+
+
+def test_host_threads_are_shared_between_local_ranks(monkeypatch):
+    from node2vec2rank_b200 import device as D
+    monkeypatch.delenv("LOCAL_WORLD_SIZE", raising=False)
+    cores = D.host_threads()
+    assert cores >= 1
+    monkeypatch.setenv("LOCAL_WORLD_SIZE", "4")
+    assert D.host_threads() == max(1, cores // 4)
+    monkeypatch.setenv("LOCAL_WORLD_SIZE", "not-a-number")
+    assert D.host_threads() == cores
