@@ -250,19 +250,24 @@ def layers_from_host(arrays, n_planes=None, transfer="auto"):
     if transfer == "auto":
         transfer = "packed" if srcs[0].numel() >= PACK_MIN_ENTRIES else "dense"
     if transfer == "packed":
-        return _layers_from_host_packed(srcs, n_planes)
+        rows, cols = srcs[0].shape
+        chunk_rows = max(1, min(rows, PACK_CHUNK_ENTRIES // max(cols, 1)))
+        try:
+            slots = _staging(chunk_rows, cols)
+        except RuntimeError:                               # no lockable host memory for the staging slots: dense copies
+            slots = None
+        if slots is not None:
+            return _layers_from_host_packed(srcs, n_planes, chunk_rows, slots)
     return _layers_from_host_dense(srcs, n_planes)
 
 
-def _layers_from_host_packed(srcs, n_planes):
+def _layers_from_host_packed(srcs, n_planes, chunk_rows, slots):
     import queue
     import threading
     dev = _dev()
     lib = N.load()
     rows, cols = srcs[0].shape
     words = (cols + 31) // 32
-    chunk_rows = max(1, min(rows, PACK_CHUNK_ENTRIES // max(cols, 1)))
-    slots = _staging(chunk_rows, cols)
     cur = torch.cuda.current_stream(dev)
     copy = torch.cuda.Stream(dev)
     dense = [torch.empty((rows, cols), dtype=torch.float32, device=dev) for _ in range(min(2, len(srcs)))]
