@@ -1,4 +1,8 @@
 """Degenerate inputs through the solver: rank-deficient, all-zero, tiny.  Prints what comes back."""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
 import torch
 from node2vec2rank_b200 import _native as N

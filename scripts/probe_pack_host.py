@@ -4,6 +4,10 @@ import os
 import sys
 import time
 
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
 
 from node2vec2rank_b200 import _native as N
