@@ -357,6 +357,19 @@ class Env:
             self.tdist.destroy_process_group()
 
 
+def allocator_counters():
+    """torch caching-allocator counters (device mallocs / frees / free-and-retry rounds so far): their change over a timed
+    region shows whether a step went to the driver for memory -- cudaMalloc and cudaFree of multi-GB blocks stall the host."""
+    import torch
+    st = torch.cuda.memory_stats()
+    return {k: int(st.get(k, 0)) for k in ("num_device_alloc", "num_device_free", "num_alloc_retries")}
+
+
+def allocator_delta(before):
+    after = allocator_counters()
+    return {k.replace("num_", ""): after[k] - before[k] for k in after}
+
+
 def transfer_note(x):
     """How the host graphs crossed PCIe in the e2e leg (device.layers_from_host.last_stats)."""
     if not x or not x.get("packed_chunks"):
@@ -449,6 +462,7 @@ def run_b200_arm(args):
     if rank == 0:
         sampler.mark()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    alloc0 = allocator_counters()
     e0.record()
     infos, launches = [], 0
     for _ in range(args.steps):
@@ -458,6 +472,7 @@ def run_b200_arm(args):
     e1.record()
     barrier()
     ms_step = reduce_max(e0.elapsed_time(e1) / max(args.steps, 1))
+    alloc_step = allocator_delta(alloc0)
     clocks = sampler.stop() if rank == 0 else None
 
     # ---- roofline of the dominant kernel (tcgen05 streaming product), measured live in the timed steps ----
@@ -492,17 +507,20 @@ def run_b200_arm(args):
         for _ in range(args.warmup):
             e2e_step()
         barrier()
+        alloc0 = allocator_counters()
         t0 = time.perf_counter()
         d2h = 0
         for _ in range(args.steps):
             d2h = e2e_step()
         barrier()
         e2e_s = reduce_max((time.perf_counter() - t0) / max(args.steps, 1))
+        alloc_e2e = allocator_delta(alloc0)
         # whole job: this rank's bytes scaled from its layers to all T (the layers have the same density)
         e2e = {"value": e2e_s, "unit": "s",
                "h2d_bytes_per_step": int(xfer.get("h2d_bytes", len(mine) * n * n * 4) * T / max(len(mine), 1)),
                "d2h_bytes_per_step": int(d2h), "host_graph_bytes_per_step": int(T) * n * n * 4,
                "host_transfer": transfer_note(xfer), "phases_per_step": phases[-args.steps:],
+               "allocator": alloc_e2e,
                "api": "N2V2R(graphs=float32 host arrays).fit_transform_rank() + aggregate_transform()"}
 
     if rank != 0:
@@ -523,7 +541,7 @@ def run_b200_arm(args):
                    "outer_iterations": last["outer_iterations"], "converged": last["converged"],
                    "angle_bound": last["angle_bound"], "setup_s": setup_s,
                    "solver_ms": last["total_ms"], "solver_stream_ms": last["stream_ms"], "solver_mma_ms": last["mma_ms"],
-                   "solver_ms_per_step": [round(i["total_ms"], 2) for i in infos],
+                   "solver_ms_per_step": [round(i["total_ms"], 2) for i in infos], "allocator": alloc_step,
                    # wall-time segments: device-side load pass per layer (select + transform + planes; untimed set-up),
                    # the solve, and the sweep (embedding gather + distances for every d + rank + Borda)
                    "segments_ms": {"preprocess_per_layer": round(preprocess_ms, 2),
