@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define N2V2R_ABI_VERSION 1
+#define N2V2R_ABI_VERSION 2
 
 typedef enum {
   N2V2R_OK = 0,
@@ -48,6 +48,8 @@ typedef enum { N2V2R_F32 = 0, N2V2R_F64 = 1 } n2v2r_dtype_t;
 typedef enum { N2V2R_EUCLIDEAN = 0, N2V2R_COSINE = 1, N2V2R_CORRELATION = 2 } n2v2r_metric_t;
 typedef enum { N2V2R_SEQUENTIAL = 0, N2V2R_ONE_VS_BEFORE = 1, N2V2R_ONE_VS_REST = 2 } n2v2r_strategy_t;
 typedef enum { N2V2R_ALGO_TCGEN05 = 0, N2V2R_ALGO_SIMT = 1 } n2v2r_algo_t;
+/* how a layer is held in HBM: dense bf16 planes, or compressed tiles (sparse layers, expanded in shared memory) */
+typedef enum { N2V2R_STORE_PLANES = 0, N2V2R_STORE_TILES = 1 } n2v2r_storage_t;
 
 int n2v2r_abi_version(void);
 const char* n2v2r_last_error(void);
@@ -112,6 +114,31 @@ int n2v2r_transpose_planes(void* stream, const void* d_planes, int n_planes, int
                            void* d_out);
 
 /* ------------------------------------------------------------------------------------
+ * K1c  compressed tiles: the storage of a SPARSE layer (after the threshold / top-percent cut of
+ * preprocessing_utils.py:127-135 most entries are zero).  Plays the role of the reference's dense ->
+ * csc_matrix conversion (N2V2R.__fit, model.py:51-53), in a form the tensor-core product can expand in
+ * shared memory.  The (n x n) matrix is cut into tiles of tile_rows x 64 (tile_rows = 128 or 256; tile
+ * (rt, kb) has index rt * ceil(n/64) + kb); a tile is a list of 8-byte entries
+ *     { u16 pos, bf16 p0, bf16 p1, bf16 p2 },   value = p0 + p1 + p2 (exact fp32),
+ * pos = element offset of (r, c) inside a K-major SWIZZLE_128B bf16 tile:
+ *     pos = (r>>3)*512 + (r&7)*64 + (((c>>3) ^ (r&7))<<3) + (c&7);
+ * lists are padded to an even number of entries with pos = 0xFFFF; d_tile_ptr[t] is the first entry of tile t,
+ * d_tile_ptr[n_tiles] the total.  Build: count (non-zeros per 128-row tile of A and of A^T, planes the values
+ * need, symmetry; synchronises) -> scan (tile_rows chosen by the caller; synchronises, returns the number of
+ * entries to allocate) -> fill (transpose=1 writes the tiles of A^T from the same dense input).
+ * ---------------------------------------------------------------------------------- */
+int n2v2r_tiles_count(void* stream, const float* d_in, int64_t n, int64_t ld,
+                      uint32_t* d_counts /* ceil(n/128) * ceil(n/64) */, uint32_t* d_counts_t /* same, for A^T */,
+                      int* h_planes, int* h_symmetric);
+int n2v2r_tiles_scan(void* stream, const uint32_t* d_counts, int64_t n, int tile_rows,
+                     uint32_t* d_tile_ptr /* ceil(n/tile_rows) * ceil(n/64) + 1 */, int64_t* h_entries);
+int n2v2r_tiles_fill(void* stream, const float* d_in, int64_t n, int64_t ld, int transpose, int tile_rows,
+                     const uint32_t* d_tile_ptr, void* d_entries /* 16-byte aligned, h_entries * 8 bytes */);
+/* d_out (n x ld_out fp32, zero-filled by the caller) = the matrix the tiles hold */
+int n2v2r_tiles_to_dense(void* stream, const uint32_t* d_tile_ptr, const void* d_entries, int64_t n, int tile_rows,
+                         float* d_out, int64_t ld_out);
+
+/* ------------------------------------------------------------------------------------
  * K2  bipartite -> unipartite projection on the tensor cores.
  * Replaces bipartite_to_unipartite_projection (preprocessing_utils.py:16-32):
  * on_rows=0: out = W^T W (cols x cols); on_rows=1: out = W W^T (rows x rows).
@@ -136,11 +163,19 @@ int n2v2r_project(void* stream, const void* d_W, int dtype, int64_t rows, int64_
  * over all processes, in place, ordered on `stream`.
  * ---------------------------------------------------------------------------------- */
 typedef struct {
-  const void* d_planes;    /* n_planes planes, each n x ld bf16                         */
+  const void* d_planes;    /* N2V2R_STORE_PLANES: n_planes planes, each n x ld bf16         */
   const void* d_planes_t;  /* planes of A^T, or NULL when the layer is symmetric         */
-  int32_t n_planes;
-  int32_t reserved;
+  int32_t n_planes;        /* planes stored (PLANES) / plane terms the values need (TILES) */
+  int32_t storage;         /* n2v2r_storage_t                                            */
   int64_t ld;
+  /* N2V2R_STORE_TILES (see "K1c compressed tiles" below) */
+  const uint32_t* d_tile_ptr;    /* n_tiles + 1 entry offsets                            */
+  const void* d_entries;         /* 8-byte entries                                       */
+  const uint32_t* d_tile_ptr_t;  /* tiles of A^T, or NULL when the layer is symmetric    */
+  const void* d_entries_t;
+  int64_t n_entries, n_entries_t;
+  int32_t tile_rows;             /* 128 or 256                                           */
+  int32_t reserved;
 } n2v2r_layer_t;
 
 typedef struct {
@@ -158,27 +193,48 @@ typedef struct {
   double tol;              /* stop when the subspace-angle bound at every checked d <= tol */
   uint64_t seed;
   const int32_t* h_check_dims; /* swept dimensions d (gap-aware stopping rule); may be NULL */
+  /* solver tuning; 0 selects the default in every field (ABI 2: these replace the former environment variables) */
+  double floor_mult;       /* residual floor as a multiple of eps32 * lambda_1 (default 0.02) */
+  double rel_floor;        /* residual target relative to lambda_j (default 8 eps32)     */
+  int32_t first_degree;    /* cap on the degree of the first filter (default 2)          */
+  int32_t no_early_lock;   /* 1 = do not lock outliers early                             */
+  int32_t trace;           /* 1 = one line per outer iteration on stderr                 */
+  int32_t comm_mode;       /* how Y is summed over the processes: 0 = `allreduce` callback, 1 = `user` is an
+                              ncclComm_t and the library calls ncclAllReduce itself on `stream` */
 } n2v2r_uase_params_t;
 
+#define N2V2R_MAX_CHECK 32
 typedef struct {
   int32_t iterations;      /* applications of the operator A A^T to the l-column block      */
   int32_t layer_passes;    /* number of (layer x skinny product) launches                */
-  int32_t converged;       /* 0 no, 1 yes, 2 residuals stagnated at the fp32 floor          */
+  int32_t converged;       /* 0 = max_iters reached; 1 = the angle bound met tol at every checked d, or every wanted
+                              residual is at its target (ARPACK's tol = 0 criterion); 2 = stopped because the residuals
+                              stagnated above the target (the fp32 floor of this matrix)                              */
   int32_t kernel_launches;
   int32_t outer_iterations;/* Rayleigh-Ritz steps                                           */
   int32_t locked;          /* Ritz pairs at the residual floor when the solver stopped      */
   double stream_ms;        /* CUDA-event time of the streaming products (split + MMA + reduce) */
   double mma_ms;           /* CUDA-event time of the tcgen05 MMA kernel launches alone      */
   int32_t mma_launches;
-  int32_t reserved;
+  int32_t bound_met;       /* 1 when the angle bound is <= tol at every checked d           */
   double total_ms;
   double stream_bytes;     /* algorithmic bytes of those launches            */
   double max_angle_bound;  /* final value of the stopping quantity                       */
   double resid[96];        /* final residual norm per Ritz pair, relative to lambda_1       */
   double ritz[96];         /* Ritz values (sigma^2), descending                          */
+  double angle_bounds[N2V2R_MAX_CHECK];  /* final Davis-Kahan bound per checked d (order of h_check_dims) */
 } n2v2r_uase_stats_t;
 
 typedef int (*n2v2r_allreduce_fn)(void* user, void* d_buf, int64_t count, int dtype, void* stream);
+
+/* NCCL communicator owned by the library (comm_mode = 1 of n2v2r_uase): the library binds the NCCL the process has
+ * already loaded (dlopen of libnccl.so.2, no link-time dependency).  One process creates the 128-byte unique id, the
+ * host side distributes it (torch.distributed broadcast, MPI, a file ...), every process calls n2v2r_comm_init with
+ * its rank; the handle is passed as `user` to n2v2r_uase.  n2v2r_comm_allreduce_f32 sums a device buffer in place. */
+int n2v2r_comm_unique_id(void* h_id128);
+int n2v2r_comm_init(const void* h_id128, int n_ranks, int rank, void** comm);
+int n2v2r_comm_destroy(void* comm);
+int n2v2r_comm_allreduce_f32(void* stream, void* comm, float* d_buf, int64_t count);
 
 size_t n2v2r_uase_workspace_bytes(const n2v2r_uase_params_t* p);
 int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2r_layer_t* h_layers,
@@ -217,6 +273,15 @@ int n2v2r_distances(void* stream, const void* d_embed, int dtype, int T, int64_t
 size_t n2v2r_rank_workspace_bytes(int64_t n, int n_cols);
 int n2v2r_rank_borda(void* stream, const double* d_scores, int64_t n, int n_cols, int n_groups,
                      int32_t* d_positions, int64_t* d_borda, void* d_ws, size_t ws_bytes);
+
+/* ------------------------------------------------------------------------------------
+ * K11b  sign transfer for the signed ranks.  Replaces signed_transform_single (model_utils.py:7-19) as
+ * N2V2R.signed_ranks_transform applies it to every column of a comparison (model.py:236-256): the score of
+ * node i keeps its sign where d_prior[i] > 0 and is negated otherwise (zero / negative / NaN priors).
+ * d_scores, d_out: (n_cols x n), float64 (is_int64 = 0) or int64 (is_int64 = 1: the Borda table); may alias.
+ * ---------------------------------------------------------------------------------- */
+int n2v2r_signed_scores(void* stream, const void* d_scores, int is_int64, int64_t n, int n_cols,
+                        const double* d_prior, void* d_out);
 
 /* ------------------------------------------------------------------------------------
  * K0b  weighted edge list -> dense symmetric matrix on the device.  Replaces

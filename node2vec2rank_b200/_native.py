@@ -27,25 +27,33 @@ class NativeError(RuntimeError):
         self.status = status
 
 
+STORE_PLANES, STORE_TILES = 0, 1
+MAX_CHECK = 32
+
+
 class Layer(C.Structure):
     _fields_ = [("d_planes", C.c_void_p), ("d_planes_t", C.c_void_p), ("n_planes", C.c_int32),
-                ("reserved", C.c_int32), ("ld", C.c_int64)]
+                ("storage", C.c_int32), ("ld", C.c_int64),
+                ("d_tile_ptr", C.c_void_p), ("d_entries", C.c_void_p), ("d_tile_ptr_t", C.c_void_p), ("d_entries_t", C.c_void_p),
+                ("n_entries", C.c_int64), ("n_entries_t", C.c_int64), ("tile_rows", C.c_int32), ("reserved", C.c_int32)]
 
 
 class UaseParams(C.Structure):
     _fields_ = [("n", C.c_int64), ("T_local", C.c_int32), ("T_global", C.c_int32), ("layer_offset", C.c_int32),
                 ("k", C.c_int32), ("l", C.c_int32), ("max_iters", C.c_int32), ("min_iters", C.c_int32),
                 ("cheb_degree", C.c_int32), ("algo", C.c_int32), ("k_chunk", C.c_int32), ("n_check", C.c_int32),
-                ("tol", C.c_double), ("seed", C.c_uint64), ("h_check_dims", C.POINTER(C.c_int32))]
+                ("tol", C.c_double), ("seed", C.c_uint64), ("h_check_dims", C.POINTER(C.c_int32)),
+                ("floor_mult", C.c_double), ("rel_floor", C.c_double), ("first_degree", C.c_int32), ("no_early_lock", C.c_int32),
+                ("trace", C.c_int32), ("comm_mode", C.c_int32)]
 
 
 class UaseStats(C.Structure):
     _fields_ = [("iterations", C.c_int32), ("layer_passes", C.c_int32), ("converged", C.c_int32),
                 ("kernel_launches", C.c_int32), ("outer_iterations", C.c_int32), ("locked", C.c_int32),
-                ("stream_ms", C.c_double), ("mma_ms", C.c_double), ("mma_launches", C.c_int32), ("reserved", C.c_int32),
+                ("stream_ms", C.c_double), ("mma_ms", C.c_double), ("mma_launches", C.c_int32), ("bound_met", C.c_int32),
                 ("total_ms", C.c_double),
                 ("stream_bytes", C.c_double), ("max_angle_bound", C.c_double),
-                ("resid", C.c_double * 96), ("ritz", C.c_double * 96)]
+                ("resid", C.c_double * 96), ("ritz", C.c_double * 96), ("angle_bounds", C.c_double * MAX_CHECK)]
 
 
 ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p)
@@ -64,16 +72,25 @@ SIGNATURES = {
     "n2v2r_planes_needed": (_i, [_vp, _vp, _i64, _i64, _i64, C.POINTER(_i)]),
     "n2v2r_is_symmetric": (_i, [_vp, _vp, _i, _i64, _i64, C.POINTER(_i)]),
     "n2v2r_transpose_planes": (_i, [_vp, _vp, _i, _i64, _i64, _vp]),
+    "n2v2r_tiles_count": (_i, [_vp, _vp, _i64, _i64, _vp, _vp, C.POINTER(_i), C.POINTER(_i)]),
+    "n2v2r_tiles_scan": (_i, [_vp, _vp, _i64, _i, _vp, C.POINTER(_i64)]),
+    "n2v2r_tiles_fill": (_i, [_vp, _vp, _i64, _i64, _i, _i, _vp, _vp]),
+    "n2v2r_tiles_to_dense": (_i, [_vp, _vp, _vp, _i64, _i, _vp, _i64]),
     "n2v2r_project_workspace_bytes": (_sz, [_i64, _i64, _i]),
     "n2v2r_project": (_i, [_vp, _vp, _i, _i64, _i64, _i64, _i, _vp, _i64, _vp, _sz]),
     "n2v2r_uase_workspace_bytes": (_sz, [C.POINTER(UaseParams)]),
     "n2v2r_uase": (_i, [_vp, C.POINTER(UaseParams), C.POINTER(Layer), _vp, _sz, ALLREDUCE_FN, _vp, _vp, _vp,
                         C.POINTER(_d), C.POINTER(UaseStats)]),
+    "n2v2r_comm_unique_id": (_i, [_vp]),
+    "n2v2r_comm_init": (_i, [_vp, _i, _i, C.POINTER(_vp)]),
+    "n2v2r_comm_destroy": (_i, [_vp]),
+    "n2v2r_comm_allreduce_f32": (_i, [_vp, _vp, _vp, _i64]),
     "n2v2r_apply_workspace_bytes": (_sz, [_i64, _i, _i]),
     "n2v2r_layer_apply": (_i, [_vp, C.POINTER(Layer), _i64, _i, _i, _vp, _vp, _i, _i, _vp, _sz]),
     "n2v2r_distances": (_i, [_vp, _vp, _i, _i, _i64, _i, C.POINTER(C.c_int32), C.POINTER(C.c_int32), _i, _i, _vp]),
     "n2v2r_rank_workspace_bytes": (_sz, [_i64, _i]),
     "n2v2r_rank_borda": (_i, [_vp, _vp, _i64, _i, _i, _vp, _vp, _vp, _sz]),
+    "n2v2r_signed_scores": (_i, [_vp, _vp, _i, _i64, _i, _vp, _vp]),
     "n2v2r_ndcg": (_i, [_vp, _vp, _i64, _i64, _vp, _i64, _vp, _vp]),
     "n2v2r_scatter_edges": (_i, [_vp, _vp, _vp, _vp, _i64, _vp, _i, _i64, _i64]),
     "n2v2r_host_pack_nonzeros": (_i, [_vp, _i64, _i64, _i64, _vp, _vp, _i64, _vp, _i, _vp]),
@@ -97,7 +114,7 @@ def load():
             fn = getattr(lib, name)            # AttributeError if the symbol is not exported
             fn.restype = res
             fn.argtypes = args
-        if lib.n2v2r_abi_version() != 1:
+        if lib.n2v2r_abi_version() != 2:
             raise ImportError("libn2v2r_b200.so ABI version mismatch")
         _lib = lib
     return _lib

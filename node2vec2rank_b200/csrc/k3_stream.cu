@@ -13,6 +13,8 @@ namespace n2v2r {
 
 int stream_apply_tcgen05(cudaStream_t s, const StreamPlan& plan, const void* planes, int n_planes, int64_t ld,
                          const float* x, __nv_bfloat16* xs, float* parts, float* out, int accumulate);  // k3_tcgen05.cu
+int stream_apply_tiles(cudaStream_t s, const StreamPlan& plan, const uint32_t* tile_ptr, const void* entries, int n_planes,
+                       int tile_rows, const float* x, __nv_bfloat16* xs, float* parts, float* out, int accumulate);   // k3_sparse.cu
 
 template <int LC>
 __global__ void __launch_bounds__(256) simt_apply_kernel(const __nv_bfloat16* __restrict__ planes, int n_planes, int64_t n,
@@ -80,6 +82,7 @@ int make_stream_plan(int64_t n, int l, int algo, int k_chunk, StreamPlan* plan) 
   plan->n_pad = round_up(n, 64);
   plan->l = l;
   plan->algo = algo;
+  plan->k_chunk_user = k_chunk > 0 ? (int)round_up(k_chunk, 64) : 0;
   if (k_chunk <= 0) k_chunk = 4096;
   k_chunk = (int)round_up(k_chunk, 64);
   plan->k_chunk = k_chunk;
@@ -96,6 +99,15 @@ int make_stream_plan(int64_t n, int l, int algo, int k_chunk, StreamPlan* plan) 
 
 int stream_apply(cudaStream_t s, const StreamPlan& plan, const n2v2r_layer_t& L, int transpose, const float* x,
                  __nv_bfloat16* xs, float* parts, float* out, int accumulate, double* bytes_moved) {
+  if (L.storage == N2V2R_STORE_TILES) {
+    const uint32_t* tp = (transpose && L.d_tile_ptr_t) ? L.d_tile_ptr_t : L.d_tile_ptr;
+    const void* en = (transpose && L.d_entries_t) ? L.d_entries_t : L.d_entries;
+    N2V2R_REQUIRE(plan.algo == N2V2R_ALGO_TCGEN05, "compressed-tile layers run on the tcgen05 path only");
+    if (bytes_moved)   // the entry lists once + tile offsets + skinny operand read + skinny result written
+      *bytes_moved += 8.0 * (double)((transpose && L.d_entries_t) ? L.n_entries_t : L.n_entries) +
+                      4.0 * (double)((plan.n + L.tile_rows - 1) / L.tile_rows) * (double)(plan.n_pad / 64) + 4.0 * plan.l * 2.0 * (double)plan.n;
+    return stream_apply_tiles(s, plan, tp, en, L.n_planes, L.tile_rows, x, xs, parts, out, accumulate);
+  }
   const void* planes = (transpose && L.d_planes_t) ? L.d_planes_t : L.d_planes;
   N2V2R_REQUIRE(planes && L.n_planes >= 1 && L.n_planes <= 3 && L.ld >= plan.n && L.ld % 64 == 0,
                 "layer: need 1..3 planes and ld a multiple of 64 >= n");

@@ -10,82 +10,10 @@
 // summed in fixed order by reduce_parts_kernel (deterministic, no atomics).
 // Plane p of a multi-plane layer multiplies only the splits s <= 2-p (terms below 2^-24 dropped).
 #include "k5_orth.cuh"
-#include <cuda.h>
-#include <cudaTypedefs.h>
+#include "tc_ptx.cuh"
 #include <vector>
 
 namespace n2v2r {
-
-// ---- PTX wrappers -------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-// Bounded wait: a protocol bug traps (error 719) after ~2 s instead of hanging the GPU box.
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  uint32_t done = 0;
-  const long long t0 = clock64();
-  while (true) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(done)
-        : "r"(bar), "r"(parity)
-        : "memory");
-    if (done) break;
-    if (clock64() - t0 > 4000000000ll) __trap();
-  }
-}
-__device__ __forceinline__ void tma_load_2d(const CUtensorMap* map, uint32_t bar, uint32_t dst, int c0, int c1) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1)
-      : "memory");
-}
-__device__ __forceinline__ void tma_load_3d(const CUtensorMap* map, uint32_t bar, uint32_t dst, int c0, int c1, int c2) {
-  asm volatile(
-      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
-      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
-      : "memory");
-}
-__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-      : "memory");
-}
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* v) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
-      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
-        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
-      : "r"(taddr));
-}
-__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
-
-// K-major, SWIZZLE_128B shared-memory matrix descriptor (rows of 128 B, 8-row groups 1024 B apart)
-__device__ __forceinline__ uint64_t sw128_desc(uint32_t saddr) {
-  return (uint64_t)((saddr & 0x3FFFFu) >> 4) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
-}
-// kind::f16 instruction descriptor: D=f32, A=B=bf16, both K-major, M=128
-__device__ __forceinline__ uint32_t idesc_bf16(int N) {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((128u >> 4) << 24);
-}
 
 struct StreamArgs {
   int n_planes, l, mh;              // planes, block width, 128-row halves per tile (1 or 2)
@@ -330,6 +258,21 @@ __global__ void __launch_bounds__(256) split_planes_kernel(const T* __restrict__
 // the sink when one is installed by the caller (uase solver / layer_apply).
 static thread_local std::vector<cudaEvent_t>* g_mma_events = nullptr;
 void set_mma_event_sink(std::vector<cudaEvent_t>* sink) { g_mma_events = sink; }
+int mma_events_begin(cudaStream_t s, cudaEvent_t* e0, cudaEvent_t* e1) {
+  *e0 = *e1 = nullptr;
+  if (!g_mma_events) return N2V2R_OK;
+  N2V2R_CUDA(cudaEventCreate(e0));
+  N2V2R_CUDA(cudaEventCreate(e1));
+  N2V2R_CUDA(cudaEventRecord(*e0, s));
+  return N2V2R_OK;
+}
+int mma_events_end(cudaStream_t s, cudaEvent_t e0, cudaEvent_t e1) {
+  if (!g_mma_events || !e0) return N2V2R_OK;
+  N2V2R_CUDA(cudaEventRecord(e1, s));
+  g_mma_events->push_back(e0);
+  g_mma_events->push_back(e1);
+  return N2V2R_OK;
+}
 
 static PFN_cuTensorMapEncodeTiled_v12000 get_encode() {
   static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
@@ -344,7 +287,7 @@ static PFN_cuTensorMapEncodeTiled_v12000 get_encode() {
 }
 
 // bf16 tensor map, SWIZZLE_128B, rank 2 or 3 (inner box = 64 elements = 128 B)
-static int make_map(CUtensorMap* map, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+int make_map(CUtensorMap* map, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                     const uint32_t* box) {
   PFN_cuTensorMapEncodeTiled_v12000 enc = get_encode();
   if (!enc) { set_error("cuTensorMapEncodeTiled entry point not available"); return N2V2R_ECUDA; }
@@ -409,19 +352,11 @@ static int launch_mma(cudaStream_t s, const void* a_planes, int n_planes, int64_
   const int n_units = a.n_tiles * a.n_splits * a.n_jb;
   const int grid = n_units < sm_count() ? n_units : sm_count();
   cudaEvent_t e0 = nullptr, e1 = nullptr;
-  if (g_mma_events) {
-    N2V2R_CUDA(cudaEventCreate(&e0));
-    N2V2R_CUDA(cudaEventCreate(&e1));
-    N2V2R_CUDA(cudaEventRecord(e0, s));
-  }
+  int rc = mma_events_begin(s, &e0, &e1);
+  if (rc) return rc;
   stream_mma_kernel<<<grid, 192, smem, s>>>(mA[0], mA[1], mA[2], mX, a);
   N2V2R_CHECK_LAUNCH();
-  if (g_mma_events) {
-    N2V2R_CUDA(cudaEventRecord(e1, s));
-    g_mma_events->push_back(e0);
-    g_mma_events->push_back(e1);
-  }
-  return N2V2R_OK;
+  return mma_events_end(s, e0, e1);
 }
 
 int stream_apply_tcgen05(cudaStream_t s, const StreamPlan& plan, const void* planes, int n_planes, int64_t ld,
@@ -433,9 +368,12 @@ int stream_apply_tcgen05(cudaStream_t s, const StreamPlan& plan, const void* pla
   rc = launch_mma(s, planes, n_planes, plan.n, ld, (size_t)plan.n * ld * sizeof(__nv_bfloat16), xs, plan.l, plan.n_pad, plan.l, 1,
                   plan.n_pad, plan.k_chunk, parts, plan.l, rows_pad * plan.l, rows_pad, plan.l);
   if (rc) return rc;
-  const int64_t total4 = plan.n * plan.l / 4;
-  reduce_parts_kernel<<<(unsigned)((total4 + 255) / 256), 256, 0, s>>>(parts, plan.n_splits, rows_pad, plan.n, plan.l, out,
-                                                                        accumulate);
+  return launch_reduce_parts(s, parts, plan.n_splits, rows_pad, plan.n, plan.l, out, accumulate);
+}
+
+int launch_reduce_parts(cudaStream_t s, const float* parts, int n_splits, int64_t rows_pad, int64_t n, int l, float* out, int accumulate) {
+  const int64_t total4 = n * l / 4;
+  reduce_parts_kernel<<<(unsigned)((total4 + 255) / 256), 256, 0, s>>>(parts, n_splits, rows_pad, n, l, out, accumulate);
   N2V2R_CHECK_LAUNCH();
   return N2V2R_OK;
 }

@@ -32,6 +32,7 @@ int launch_axpbypcz(cudaStream_t s, float* out, const float* x, double a, const 
 struct StreamPlan {
   int64_t n, n_pad;
   int l, algo, k_chunk, n_splits;
+  int k_chunk_user;                // K chunk fixed by the caller (0 = kernel picks)
   size_t xs_bytes, part_bytes;     // split-transposed operand, K-split partial sums
 };
 void set_mma_event_sink(std::vector<cudaEvent_t>* sink);   // k3_tcgen05.cu: time every MMA launch (nullptr = off)

@@ -2,6 +2,7 @@
 // Replaces model.py:57-96 (__rank), model_utils.py:39-67 (compute_pairwise_distances),
 // model.py:167-185 + model_utils.py:22-36 (descending sort + Borda points).
 #include "common.cuh"
+#include <algorithm>
 #include <math.h>
 
 namespace n2v2r {
@@ -192,9 +193,33 @@ __global__ void __launch_bounds__(256) ndcg_kernel(const int32_t* __restrict__ r
   }
 }
 
+// ---- signed ranks: out = prior > 0 ? score : -score, per node, for every column (model_utils.py:7-19) ----
+template <class T>
+__global__ void __launch_bounds__(256) signed_scores_kernel(const T* __restrict__ scores, int64_t n, int64_t total,
+                                                            const double* __restrict__ prior, T* __restrict__ out) {
+  for (int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+    const T v = scores[e];
+    out[e] = prior[e % n] > 0.0 ? v : -v;          // zero, negative and NaN priors take the negative branch, like the reference
+  }
+}
+
 }  // namespace n2v2r
 
 using namespace n2v2r;
+
+extern "C" int n2v2r_signed_scores(void* stream, const void* d_scores, int is_int64, int64_t n, int n_cols, const double* d_prior,
+                                   void* d_out) {
+  N2V2R_REQUIRE(d_scores && d_prior && d_out, "signed_scores: null pointer");
+  N2V2R_REQUIRE(n > 0 && n_cols >= 0, "signed_scores: bad shape");
+  if (n_cols == 0) return N2V2R_OK;
+  cudaStream_t s = (cudaStream_t)stream;
+  const int64_t total = n * n_cols;
+  const unsigned grid = (unsigned)std::min<int64_t>((total + 255) / 256, (int64_t)sm_count() * 16);
+  if (is_int64) signed_scores_kernel<long long><<<grid, 256, 0, s>>>((const long long*)d_scores, n, total, d_prior, (long long*)d_out);
+  else signed_scores_kernel<double><<<grid, 256, 0, s>>>((const double*)d_scores, n, total, d_prior, (double*)d_out);
+  N2V2R_CHECK_LAUNCH();
+  return N2V2R_OK;
+}
 
 extern "C" int n2v2r_distances(void* stream, const void* d_embed, int dtype, int T, int64_t n, int k,
                                const int32_t* h_col_dim, const int32_t* h_col_metric, int n_cols,

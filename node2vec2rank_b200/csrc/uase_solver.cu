@@ -22,12 +22,13 @@
 #include "k5_orth.cuh"
 #include <float.h>
 #include <math.h>
-#include <stdlib.h>
 #include <string.h>
 #include <vector>
 #include <algorithm>
 
 namespace n2v2r {
+
+int comm_allreduce_f32(void* comm, float* d_buf, int64_t count, cudaStream_t s);   // comm.cu
 
 struct SolverBufs {
   float *Q, *Y, *Qn, *Qw, *X0, *X1, *X2, *Zt;
@@ -93,7 +94,8 @@ extern "C" int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2
                           n2v2r_uase_stats_t* st) {
   RC(check_params(p));
   N2V2R_REQUIRE(L && d_ws && d_embed && h_sigma, "uase: null pointer");
-  N2V2R_REQUIRE(allreduce || p->T_local == p->T_global, "uase: sharded layers need an all-reduce callback");
+  N2V2R_REQUIRE(allreduce || p->T_local == p->T_global || (p->comm_mode == 1 && user),
+                "uase: sharded layers need an all-reduce callback or an NCCL communicator (comm_mode = 1)");
   cudaStream_t s = (cudaStream_t)stream;
   StreamPlan plan;
   RC(make_stream_plan(p->n, p->l, p->algo, p->k_chunk, &plan));
@@ -103,17 +105,15 @@ extern "C" int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2
   const int l = p->l, k = p->k, T = p->T_local;
   const size_t nl = (size_t)n * l;
   const int m_cap = p->cheb_degree <= 0 ? 32 : p->cheb_degree;
-  double floor_mult = 0.02, rel_floor = 8.0 * (double)FLT_EPSILON;   // residual target: 8 eps32 lam_j (measured fp32 floor ~ eps32 lam_j)
-  if (const char* ev = getenv("N2V2R_FLOOR_MULT")) floor_mult = atof(ev);     // developer knobs (scripts/probe_solver.py)
-  if (const char* ev = getenv("N2V2R_REL_FLOOR")) rel_floor = atof(ev);
-  const bool trace = getenv("N2V2R_TRACE") != nullptr;
+  // residual target: 8 eps32 lam_j (measured fp32 floor ~ eps32 lam_j); tuning comes through the params (0 = default)
+  const double floor_mult = p->floor_mult > 0.0 ? p->floor_mult : 0.02;
+  const double rel_floor = p->rel_floor > 0.0 ? p->rel_floor : 8.0 * (double)FLT_EPSILON;
+  const bool trace = p->trace != 0;
   // The Ritz values of the random start block say nothing about outliers (C3: lam_1 is estimated 500x too small), so the
-  // growth cap below cannot protect the first filter: its degree is limited to 2.  (N2V2R_FIRST_DEGREE: developer knob.)
-  int first_cap = 2;
-  if (const char* ev = getenv("N2V2R_FIRST_DEGREE")) first_cap = atoi(ev);
-  const bool early_lock = getenv("N2V2R_NO_EARLY_LOCK") == nullptr;
-  double need_extra = 1.0;
-  if (const char* ev = getenv("N2V2R_NEED_EXTRA")) need_extra = atof(ev);
+  // growth cap below cannot protect the first filter: its degree is limited to 2.
+  const int first_cap = p->first_degree > 0 ? p->first_degree : 2;
+  const bool early_lock = p->no_early_lock == 0;
+  const double need_extra = 1.0;
   const double rho_max = 1e4;            // cap on T_m(x_unlocked)/T_m(x_k): keeps every fp32 column dominated by its own Ritz vector
   n2v2r_uase_stats_t stats;
   memset(&stats, 0, sizeof(stats));
@@ -150,7 +150,9 @@ extern "C" int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2
     stats.layer_passes += 2 * T;
     stats.kernel_launches += 2 * T * per_pass;
     stats.iterations += 1;
-    if (allreduce && allreduce(user, out, (int64_t)nl, N2V2R_F32, stream) != 0) {
+    if (p->comm_mode == 1 && user && p->T_local != p->T_global) {
+      RC(comm_allreduce_f32(user, out, (int64_t)nl, s));
+    } else if (allreduce && allreduce(user, out, (int64_t)nl, N2V2R_F32, stream) != 0) {
       set_error("uase: all-reduce callback failed (Y)");
       return N2V2R_ECOMM;
     }
@@ -172,7 +174,8 @@ extern "C" int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2
   std::vector<double> lam(l), res(l);
   double bound = INFINITY;
   int locked = 0, outer = 0, stalls = 0;
-  bool converged = false, stagnated = false, last_filtered = false;
+  bool converged = false, stagnated = false, last_filtered = false, bound_met = false, floor_met = false;
+  std::vector<double> dim_bounds(N2V2R_MAX_CHECK, 0.0);
   double best_worst = INFINITY, prev_worst = INFINITY, predicted_gain = 1.0;
   while (true) {
     ++outer;
@@ -200,10 +203,15 @@ extern "C" int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2
     if (p->h_check_dims && p->n_check > 0) {
       for (int c = 0; c < p->n_check; ++c) {
         const int d = p->h_check_dims[c];
-        if (d >= 1 && d <= k) bound = std::max(bound, angle_bound(d));
+        if (d >= 1 && d <= k) {
+          const double bd = angle_bound(d);
+          bound = std::max(bound, bd);
+          if (c < N2V2R_MAX_CHECK) dim_bounds[c] = bd;
+        }
       }
     } else {
       bound = angle_bound(k);
+      dim_bounds[0] = bound;
     }
     const double floor_ = floor_mult * (double)FLT_EPSILON * std::max(lam[0], 0.0);
     auto target = [&](int j) { return std::max(floor_, rel_floor * lam[j]); };
@@ -238,7 +246,9 @@ extern "C" int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2
     }
     best_worst = std::min(best_worst, worst);
     prev_worst = worst;
-    converged = (bound <= p->tol) || all_floor || stagnated;
+    bound_met = bound <= p->tol;
+    floor_met = all_floor;
+    converged = bound_met || all_floor || stagnated;
     last_filtered = false;
     if ((converged && stats.iterations >= p->min_iters) || stats.iterations >= p->max_iters) break;
     // ---- filter degree ----------------------------------------------------------------------
@@ -328,8 +338,10 @@ extern "C" int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2
   cudaEventDestroy(ev_all0); cudaEventDestroy(ev_all1);
   stats.outer_iterations = outer;
   stats.locked = locked;
-  stats.converged = converged ? (stagnated && !(bound <= p->tol) ? 2 : 1) : 0;   // 2 = stopped at the fp32 residual floor
+  stats.converged = converged ? ((bound_met || floor_met) ? 1 : 2) : 0;   // 2 = residuals stagnated above the target
+  stats.bound_met = bound_met ? 1 : 0;
   stats.max_angle_bound = bound;
+  for (int c = 0; c < N2V2R_MAX_CHECK; ++c) stats.angle_bounds[c] = dim_bounds[c];
   for (int j = 0; j < l && j < 96; ++j) {
     stats.ritz[j] = lam[j];
     stats.resid[j] = lam[0] > 0 ? res[j] / lam[0] : 0.0;     // residual norms relative to lam_1

@@ -22,8 +22,9 @@ def _dev():
 
 @dataclass
 class DeviceLayer:
-    """A preprocessed graph layer resident in HBM as bf16 planes (see include/n2v2r_b200.h)."""
-    planes: torch.Tensor            # (P, n, ld) bf16
+    """A preprocessed graph layer resident in HBM (see include/n2v2r_b200.h): dense bf16 planes, or -- for sparse
+    layers -- compressed tiles that the product kernel expands in shared memory (storage == "tiles")."""
+    planes: torch.Tensor | None     # (P, n, ld) bf16, None for a tiles layer
     n: int
     ld: int
     n_planes: int
@@ -31,17 +32,38 @@ class DeviceLayer:
     planes_t: torch.Tensor | None = None
     colsum: torch.Tensor | None = None     # (n,) float64, column sums of the fp32 values
     shape: tuple = field(default=())
+    storage: str = "planes"
+    tile_rows: int = 0
+    tile_ptr: torch.Tensor | None = None   # (n_tiles + 1,) int32 (uint32 offsets)
+    entries: torch.Tensor | None = None    # (n_entries, 2) int32: 8-byte entries
+    tile_ptr_t: torch.Tensor | None = None
+    entries_t: torch.Tensor | None = None
     dtype = np.float32
 
     def __post_init__(self):
         self.shape = (self.n, self.n)
 
+    @property
+    def device(self):
+        return (self.planes if self.planes is not None else self.tile_ptr).device
+
     def c_struct(self):
+        if self.storage == "tiles":
+            return N.Layer(0, 0, self.n_planes, N.STORE_TILES, self.ld,
+                           self.tile_ptr.data_ptr(), self.entries.data_ptr(),
+                           0 if self.tile_ptr_t is None else self.tile_ptr_t.data_ptr(),
+                           0 if self.entries_t is None else self.entries_t.data_ptr(),
+                           self.entries.shape[0], 0 if self.entries_t is None else self.entries_t.shape[0], self.tile_rows, 0)
         return N.Layer(self.planes.data_ptr(), 0 if self.planes_t is None else self.planes_t.data_ptr(),
-                       self.n_planes, 0, self.ld)
+                       self.n_planes, N.STORE_PLANES, self.ld, 0, 0, 0, 0, 0, 0, 0, 0)
 
     def to_dense(self):
-        """fp32 (n, n) device tensor reconstructed from the planes (exact for P planes)."""
+        """fp32 (n, n) device tensor reconstructed from the stored form (exact)."""
+        if self.storage == "tiles":
+            out = torch.zeros((self.n, self.n), dtype=torch.float32, device=self.device)
+            N.check(N.load().n2v2r_tiles_to_dense(N.stream_ptr(), N.ptr(self.tile_ptr), N.ptr(self.entries), self.n, self.tile_rows,
+                                                  N.ptr(out), self.n))
+            return out
         return self.planes[:, :, :self.n].to(torch.float32).sum(dim=0)
 
     def numpy(self):
@@ -53,6 +75,8 @@ class DeviceLayer:
 
     @property
     def nbytes(self):
+        if self.storage == "tiles":
+            return sum(t.numel() * t.element_size() for t in (self.tile_ptr, self.entries, self.tile_ptr_t, self.entries_t) if t is not None)
         return self.planes.numel() * 2 * (2 if self.planes_t is not None else 1)
 
 
@@ -188,14 +212,66 @@ def project(W: torch.Tensor, on):
     return out
 
 
-def make_layer(x32: torch.Tensor, n_planes=None, colsum=None, check_symmetry=True):
-    """fp32 (n, n) device matrix -> DeviceLayer (planes + symmetry flag / transposed copy)."""
+TILES_MAX_DENSITY = 0.08        # layers sparser than this are stored as compressed tiles (storage="auto")
+TILES_MIN_N = 4096              # ... when they are large enough for the streaming product to matter
+
+
+def make_tiles_layer(x32: torch.Tensor, colsum=None, max_density=None):
+    """fp32 (n, n) device matrix -> DeviceLayer(storage="tiles"), or (None, planes, symmetric) when the matrix is denser
+    than `max_density` (the caller then builds planes; the count pass has already told it how many and the symmetry)."""
     lib = N.load()
     n = x32.shape[0]
+    assert x32.dim() == 2 and x32.shape[0] == x32.shape[1] and x32.dtype == torch.float32, "layer must be a square float32 matrix"
+    if x32.stride(1) != 1:
+        x32 = x32.contiguous()
+    dev = x32.device
+    n_kb, n_rt128 = (n + 63) // 64, (n + 127) // 128
+    counts = torch.empty((2, n_rt128 * n_kb), dtype=torch.int32, device=dev)
+    planes, sym = C.c_int(1), C.c_int(1)
+    N.check(lib.n2v2r_tiles_count(N.stream_ptr(), N.ptr(x32), n, x32.stride(0), N.ptr(counts[0]), N.ptr(counts[1]),
+                                  C.byref(planes), C.byref(sym)))
+    P = planes.value
+    tile_rows = 256 if P <= 2 else 128
+    n_tiles = ((n + tile_rows - 1) // tile_rows) * n_kb
+
+    def build(which, transpose):
+        tp = torch.empty(n_tiles + 1, dtype=torch.int32, device=dev)
+        total = C.c_int64(0)
+        N.check(lib.n2v2r_tiles_scan(N.stream_ptr(), N.ptr(counts[which]), n, tile_rows, N.ptr(tp), C.byref(total)))
+        if max_density is not None and total.value > max_density * n * n:
+            return None, None
+        ent = torch.empty((max(total.value, 2), 2), dtype=torch.int32, device=dev)
+        N.check(lib.n2v2r_tiles_fill(N.stream_ptr(), N.ptr(x32), n, x32.stride(0), int(transpose), tile_rows, N.ptr(tp), N.ptr(ent)))
+        return tp, ent[: total.value]
+
+    tp, ent = build(0, False)
+    if tp is None:
+        return None, P, bool(sym.value)
+    tp_t = ent_t = None
+    if not sym.value:
+        tp_t, ent_t = build(1, True)
+    return DeviceLayer(planes=None, n=n, ld=(n + 63) // 64 * 64, n_planes=P, symmetric=bool(sym.value), colsum=colsum,
+                       storage="tiles", tile_rows=tile_rows, tile_ptr=tp, entries=ent, tile_ptr_t=tp_t, entries_t=ent_t), P, bool(sym.value)
+
+
+def make_layer(x32: torch.Tensor, n_planes=None, colsum=None, check_symmetry=True, storage="auto"):
+    """fp32 (n, n) device matrix -> DeviceLayer: compressed tiles when the matrix is sparse (storage "auto": density <=
+    TILES_MAX_DENSITY and n >= TILES_MIN_N; "tiles": always), else bf16 planes + symmetry flag / transposed copy."""
+    n = x32.shape[0]
     assert x32.shape[0] == x32.shape[1], "layer must be square"
+    if storage not in ("auto", "planes", "tiles"):
+        raise ValueError(f"unknown layer storage {storage!r}")
+    known_sym = None
+    if storage == "tiles" or (storage == "auto" and n >= TILES_MIN_N and n_planes is None):
+        layer, P, known_sym = make_tiles_layer(x32, colsum=colsum, max_density=None if storage == "tiles" else TILES_MAX_DENSITY)
+        if layer is not None:
+            if layer.colsum is None:
+                layer.colsum = x32.sum(dim=0, dtype=torch.float64)
+            return layer
+        n_planes = n_planes or P
     P = n_planes or planes_needed(x32)
     _, planes, ld_p, cs = transform(x32, n_planes=P, want_colsum=colsum is None)
-    return finish_layer(planes, n, ld_p, P, cs if colsum is None else colsum, check_symmetry)
+    return finish_layer(planes, n, ld_p, P, cs if colsum is None else colsum, check_symmetry, known_symmetric=known_sym)
 
 
 PACK_MIN_ENTRIES = 4_000_000          # below this a layer crosses PCIe dense (the packed pipeline has fixed costs)
@@ -229,7 +305,7 @@ def _staging(chunk_rows, cols):
     return _pack_staging[key]
 
 
-def layers_from_host(arrays, n_planes=None, transfer="auto"):
+def layers_from_host(arrays, n_planes=None, transfer="auto", storage="auto"):
     """float32 (n, n) host matrices (what the reference's DataLoader hands to N2V2R) -> DeviceLayers.
 
     transfer = "dense": double-buffered H2D of the dense matrices (the copy of layer t+1 runs on a copy stream while
@@ -257,11 +333,11 @@ def layers_from_host(arrays, n_planes=None, transfer="auto"):
         except RuntimeError:                               # no lockable host memory for the staging slots: dense copies
             slots = None
         if slots is not None:
-            return _layers_from_host_packed(srcs, n_planes, chunk_rows, slots)
-    return _layers_from_host_dense(srcs, n_planes)
+            return _layers_from_host_packed(srcs, n_planes, chunk_rows, slots, storage)
+    return _layers_from_host_dense(srcs, n_planes, storage)
 
 
-def _layers_from_host_packed(srcs, n_planes, chunk_rows, slots):
+def _layers_from_host_packed(srcs, n_planes, chunk_rows, slots, storage="auto"):
     import queue
     import threading
     dev = _dev()
@@ -338,7 +414,7 @@ def _layers_from_host_packed(srcs, n_planes, chunk_rows, slots):
             if isinstance(ev, BaseException):
                 raise ev
             cur.wait_event(ev)
-            layers.append(make_layer(dense[t % 2], n_planes=n_planes))
+            layers.append(make_layer(dense[t % 2], n_planes=n_planes, storage=storage))
             done = torch.cuda.Event()
             done.record(cur)
             consumed.put(done)
@@ -348,13 +424,13 @@ def _layers_from_host_packed(srcs, n_planes, chunk_rows, slots):
         raise
     finally:
         worker.join()
-    cur.wait_stream(copy)
+        cur.wait_stream(copy)          # also on the error path: the buffers go back to the allocator only after the copy stream
     stats["total_s"] = time.perf_counter() - t_begin
     layers_from_host.last_stats = stats
     return layers
 
 
-def _layers_from_host_dense(srcs, n_planes):
+def _layers_from_host_dense(srcs, n_planes, storage="auto"):
     dev = _dev()
     t_begin = time.perf_counter()
     stats = dict(packed_chunks=0, dense_chunks=len(srcs), h2d_bytes=sum(x.numel() * 4 for x in srcs), total_s=0.0)
@@ -380,19 +456,22 @@ def _layers_from_host_dense(srcs, n_planes):
         if t + 1 < len(srcs):
             issue(t + 1)
         cur.wait_event(copied[t])
-        layers.append(make_layer(bufs[t % 2], n_planes=n_planes))
+        layers.append(make_layer(bufs[t % 2], n_planes=n_planes, storage=storage))
         built[t].record(cur)
     cur.wait_stream(copy)
     stats["total_s"] = time.perf_counter() - t_begin        # host time: the last load pass may still be running
     return layers
 
 
-def finish_layer(planes, n, ld_p, P, colsum, check_symmetry=True):
+def finish_layer(planes, n, ld_p, P, colsum, check_symmetry=True, known_symmetric=None):
     lib = N.load()
     sym = C.c_int(1)
     planes_t = None
     if check_symmetry:
-        N.check(lib.n2v2r_is_symmetric(N.stream_ptr(), N.ptr(planes), P, n, ld_p, C.byref(sym)))
+        if known_symmetric is not None:
+            sym = C.c_int(int(known_symmetric))
+        else:
+            N.check(lib.n2v2r_is_symmetric(N.stream_ptr(), N.ptr(planes), P, n, ld_p, C.byref(sym)))
         if not sym.value:
             planes_t = torch.empty_like(planes)
             N.check(lib.n2v2r_transpose_planes(N.stream_ptr(), N.ptr(planes), P, n, ld_p, N.ptr(planes_t)))
@@ -400,7 +479,7 @@ def finish_layer(planes, n, ld_p, P, colsum, check_symmetry=True):
 
 
 def preprocess_to_layer(x: torch.Tensor, threshold=None, top_percent_keep=100, binarize=False, absolute=False,
-                        project_unipartite_on="columns", storage_planes=None, want_f32=False):
+                        project_unipartite_on="columns", storage_planes=None, want_f32=False, storage="auto"):
     """network_transform (preprocessing_utils.py:116-141) on the device.
 
     Returns (DeviceLayer, out_f32 | None).  Order of operations as the reference: abs ->
@@ -423,37 +502,49 @@ def preprocess_to_layer(x: torch.Tensor, threshold=None, top_percent_keep=100, b
         cut = percentile_cut(x, 100 - top_percent_keep, absolute, threshold)
     n = x.shape[0]
     check_sym = not projected            # K2 mirrors the upper triangle: W^T W is exactly symmetric, and K1b is elementwise
-    if binarize:
+    if binarize and storage != "tiles":
         P = 1
-    elif storage_planes:
+    elif storage_planes and storage != "tiles":
         P = int(storage_planes)
     else:
         P = 0
     if P == 0:
         # exact storage: materialise fp32 once, count the planes it needs, then split
         if cut is None and not binarize and not absolute and threshold is None:
-            layer = make_layer(x, check_symmetry=check_sym)          # identity transform: split the projected matrix directly
+            layer = make_layer(x, check_symmetry=check_sym, storage=storage)   # identity transform: store the projected matrix directly
             return layer, (x if want_f32 else None)
         out, _, _, cs = transform(x, absolute, threshold, cut, binarize, want_f32=True, want_colsum=True)
-        layer = make_layer(out, colsum=cs, check_symmetry=check_sym)
+        layer = make_layer(out, colsum=cs, check_symmetry=check_sym, storage=storage)
         return layer, (out if want_f32 else None)
     out, planes, ld_p, cs = transform(x, absolute, threshold, cut, binarize, want_f32=want_f32, n_planes=P,
                                       want_colsum=True)
     return finish_layer(planes, n, ld_p, P, cs, check_sym), out
 
 
+CONVERGED_STATUS = {0: "max_iters", 1: "converged", 2: "stagnated"}
+
+
 def uase(layers, k, l=64, tol=1e-5, max_iters=300, min_iters=2, seed=42, check_dims=None, algo=N.ALGO_TCGEN05,
-         k_chunk=0, allreduce=None, T_global=None, layer_offset=0, want_left=False, cheb_degree=0, group=None):
-    """K3-K8: returns (embeddings (T_local, n, k) fp32 device, sigma (k,) float64, left | None, stats dict)."""
+         k_chunk=0, allreduce=None, T_global=None, layer_offset=0, want_left=False, cheb_degree=0, group=None,
+         floor_mult=0.0, rel_floor=0.0, first_degree=0, no_early_lock=False, trace=False):
+    """K3-K8: returns (embeddings (T_local, n, k) fp32 device, sigma (k,) float64, left | None, stats dict).
+
+    stats["converged"] is the solver's tri-state (0 = max_iters reached, 1 = angle bound <= tol at every checked d or every
+    wanted residual at its target, 2 = stopped because the residuals stagnated above the target), stats["converged_status"]
+    its name, stats["bound_met"] whether the Davis-Kahan bound met `tol`, stats["angle_bounds"] the bound per checked d."""
     lib = N.load()
     dev = _dev()
     T = len(layers)
     n = layers[0].n
     dims = np.asarray(sorted(set(int(d) for d in (check_dims or [k]) if 1 <= int(d) <= k)), dtype=np.int32)
+    if len(dims) > N.MAX_CHECK:
+        dims = dims[-N.MAX_CHECK:]
     p = N.UaseParams(n=n, T_local=T, T_global=T_global or T, layer_offset=layer_offset, k=k, l=l,
                      max_iters=max_iters, min_iters=min_iters, cheb_degree=cheb_degree, algo=algo, k_chunk=k_chunk,
                      n_check=len(dims), tol=tol, seed=seed,
-                     h_check_dims=dims.ctypes.data_as(C.POINTER(C.c_int32)))
+                     h_check_dims=dims.ctypes.data_as(C.POINTER(C.c_int32)),
+                     floor_mult=float(floor_mult), rel_floor=float(rel_floor), first_degree=int(first_degree),
+                     no_early_lock=int(bool(no_early_lock)), trace=int(bool(trace)), comm_mode=0)
     ws_bytes = lib.n2v2r_uase_workspace_bytes(C.byref(p))
     if ws_bytes == 0:
         raise N.NativeError(N.EINVAL, lib.n2v2r_last_error().decode())
@@ -464,25 +555,53 @@ def uase(layers, k, l=64, tol=1e-5, max_iters=300, min_iters=2, seed=42, check_d
     stats = N.UaseStats()
     arr = (N.Layer * T)(*[L.c_struct() for L in layers])
     state = None
+    user = None
     if allreduce is not None:
         cb = N.ALLREDUCE_FN(allreduce)
     elif (T_global or T) > T:                    # layer-sharded: all-reduce Y over the ranks (dist.py)
         from . import dist
-        cb, state = dist.make_allreduce_callback(ws, group)
+        comm = dist.native_comm(group)
+        if comm is not None:                     # ncclAllReduce issued by the library itself, no Python in the solver loop
+            p.comm_mode = 1
+            user = comm
+            cb = C.cast(None, N.ALLREDUCE_FN)
+        else:
+            cb, state = dist.make_allreduce_callback(ws, group)
     else:
         cb = C.cast(None, N.ALLREDUCE_FN)
-    rc = lib.n2v2r_uase(N.stream_ptr(), C.byref(p), arr, N.ptr(ws), ws_bytes, cb, None, N.ptr(emb), N.ptr(left),
+    rc = lib.n2v2r_uase(N.stream_ptr(), C.byref(p), arr, N.ptr(ws), ws_bytes, cb, user, N.ptr(emb), N.ptr(left),
                         sigma.ctypes.data_as(C.POINTER(C.c_double)), C.byref(stats))
     if state is not None and state["error"] is not None:
         raise state["error"]
     N.check(rc, allow=(N.ENOTCONV,))
-    info = dict(allreduce_calls=0 if state is None else state["calls"], allreduce_bytes=0 if state is None else state["bytes"],
-                iterations=stats.iterations, layer_passes=stats.layer_passes, converged=bool(stats.converged),
+    info = dict(allreduce_calls=(stats.iterations if p.comm_mode == 1 else 0) if state is None else state["calls"],
+                allreduce_bytes=(stats.iterations * n * l * 4 if p.comm_mode == 1 else 0) if state is None else state["bytes"],
+                allreduce_path="nccl-native" if p.comm_mode == 1 else ("callback" if state is not None else "none"),
+                iterations=stats.iterations, layer_passes=stats.layer_passes, converged=int(stats.converged),
+                converged_status=CONVERGED_STATUS.get(int(stats.converged), "?"), bound_met=bool(stats.bound_met),
                 kernel_launches=stats.kernel_launches, outer_iterations=stats.outer_iterations,
                 locked=stats.locked, stream_ms=stats.stream_ms, mma_ms=stats.mma_ms, mma_launches=stats.mma_launches, total_ms=stats.total_ms,
                 stream_bytes=stats.stream_bytes, angle_bound=stats.max_angle_bound,
+                angle_bounds={int(d): float(stats.angle_bounds[i]) for i, d in enumerate(dims)},
                 resid=np.asarray(stats.resid[:l]), ritz=np.asarray(stats.ritz[:l]), status=rc, l=l)
     return emb, sigma, left, info
+
+
+def subspace_sin_angles(emb_a: torch.Tensor, emb_b: torch.Tensor, dims):
+    """sin of the largest principal angle between span(V_a[:, :d]) and span(V_b[:, :d]) for every d in dims, V = the
+    stacked (T n x k) embeddings of two solves.  A CHECKER (bench / tests), not on the hot path: three k x k Gram matrices
+    accumulated in float64 on the device (torch), the rest on the host -- exact enough to resolve 1e-7 on fp32 data."""
+    a = emb_a.reshape(-1, emb_a.shape[-1]).double()
+    b = emb_b.reshape(-1, emb_b.shape[-1]).double()
+    Saa, Sbb, Sab = (a.T @ a).cpu().numpy(), (b.T @ b).cpu().numpy(), (a.T @ b).cpu().numpy()
+    out = {}
+    for d in dims:
+        La, Lb = np.linalg.cholesky(Saa[:d, :d]), np.linalg.cholesky(Sbb[:d, :d])
+        Cm = np.linalg.solve(La, Sab[:d, :d])
+        Cm = np.linalg.solve(Lb, Cm.T).T                       # Qa^T Qb with Q = V L^-T
+        cos_min = np.linalg.svd(Cm, compute_uv=False).min()
+        out[int(d)] = float(np.sqrt(max(0.0, 1.0 - min(1.0, cos_min) ** 2)))
+    return out
 
 
 def layer_apply(layer: DeviceLayer, x: torch.Tensor, transpose=False, algo=N.ALGO_TCGEN05, k_chunk=0, ws=None):
@@ -547,6 +666,22 @@ def rank_borda(scores: torch.Tensor, want_positions=False):
     return borda[0], (pos[0] if pos is not None else None)
 
 
+def signed_scores(scores: torch.Tensor, prior: torch.Tensor):
+    """K11b: scores (cols, n) float64 or int64, prior (n,) float64 -> same shape/dtype, sign taken from the prior
+    (kept where prior > 0, negated otherwise; model_utils.py:7-19)."""
+    lib = N.load()
+    if scores.dtype not in (torch.float64, torch.int64):
+        raise TypeError("signed_scores expects float64 or int64 scores")
+    scores = scores.contiguous()
+    prior = prior.to(torch.float64).contiguous()
+    cols, n = scores.shape
+    if prior.numel() != n:
+        raise ValueError("prior and scores disagree on the number of nodes")
+    out = torch.empty_like(scores)
+    N.check(lib.n2v2r_signed_scores(N.stream_ptr(), N.ptr(scores), int(scores.dtype == torch.int64), n, cols, N.ptr(prior), N.ptr(out)))
+    return out
+
+
 MAX_EMBED_DIM = 72        # block width l <= 80 (TMEM holds two 3l-column accumulators) minus at least 8 guard vectors
 
 
@@ -561,4 +696,6 @@ def default_block_width(k, n):
 
 def column_sums(layer: DeviceLayer):
     """Column sums (float64, device) of a DeviceLayer: sum over planes of the bf16 values (model.py:293-294)."""
+    if layer.storage == "tiles":
+        return layer.to_dense().sum(dim=0, dtype=torch.float64)
     return layer.planes[:, :, :layer.n].to(torch.float64).sum(dim=(0, 1))

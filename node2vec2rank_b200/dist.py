@@ -63,6 +63,46 @@ def make_allreduce_callback(workspace: torch.Tensor, group=None):
     return N.ALLREDUCE_FN(_cb), state
 
 
+_native_comms = {}
+
+
+def native_comm(group=None):
+    """ncclComm_t (as a ctypes void pointer) of a communicator the C library owns, spanning the ranks of `group`, or None
+    when the process group is not NCCL (gloo in the CPU tests) / not initialised.  Created once per group: rank 0 draws the
+    unique id, torch.distributed broadcasts its 128 bytes, every rank calls n2v2r_comm_init.  With it the solver issues
+    ncclAllReduce itself (comm_mode = 1) and no Python runs inside the solver loop."""
+    import os
+    if not is_distributed() or os.environ.get("N2V2R_ALLREDUCE", "native") != "native":
+        return None
+    try:
+        if torch.distributed.get_backend(group) != "nccl":
+            return None
+    except Exception:
+        return None
+    key = id(group) if group is not None else 0
+    if key not in _native_comms:
+        lib = N.load()
+        world, rank = torch.distributed.get_world_size(group), torch.distributed.get_rank(group)
+        buf = (C.c_ubyte * 128)()
+        if rank == 0:
+            N.check(lib.n2v2r_comm_unique_id(buf))
+        t = torch.tensor(list(buf), dtype=torch.uint8, device=N.require_gpu())
+        src = torch.distributed.get_global_rank(group, 0) if group is not None else 0
+        torch.distributed.broadcast(t, src=src, group=group)
+        raw = bytes(t.cpu().tolist())
+        comm = C.c_void_p()
+        N.check(lib.n2v2r_comm_init(raw, world, rank, C.byref(comm)))
+        _native_comms[key] = comm
+    return _native_comms[key]
+
+
+def destroy_native_comms():
+    lib = N.load()
+    for comm in _native_comms.values():
+        lib.n2v2r_comm_destroy(comm)
+    _native_comms.clear()
+
+
 def gather_layers(local: torch.Tensor, T, group=None):
     """All-gather the per-layer blocks (T_local, n, k) of every rank into (T, n, k), in layer order."""
     world = torch.distributed.get_world_size(group)
@@ -91,4 +131,4 @@ def gather_blocks(local: torch.Tensor, total, group=None):
     return gather_layers(flat, total, group).reshape((total,) + tail)
 
 
-__all__ = ["is_distributed", "layer_partition", "make_allreduce_callback", "gather_layers", "gather_blocks"]
+__all__ = ["is_distributed", "layer_partition", "make_allreduce_callback", "native_comm", "destroy_native_comms", "gather_layers", "gather_blocks"]

@@ -10,6 +10,8 @@ Additive, optional config keys (defaults keep reference behaviour):
   block_width (int, default: max dim + >=24 guard vectors rounded up to 16): solver block l
   solver_tol (float, default 1e-5), solver_max_iters (int, default 400)
   storage_planes (int | None): bf16 planes per weighted layer (None = exact)
+  layer_storage ("auto" | "planes" | "tiles", default "auto"): dense bf16 planes, or compressed tiles for sparse
+      layers (device.make_layer); "auto" picks tiles for large layers under 8 % density
   layer_sharded (bool, default False): under torch.distributed (one process per GPU) `graphs` holds only
       this rank's contiguous block of layers (dist.layer_partition); Y is all-reduced per operator
       application, embeddings are all-gathered, every rank returns the full tables
@@ -30,7 +32,26 @@ import torch
 from . import _native as N
 from . import device as D
 from . import dist
-from .model_utils import signed_transform_single
+
+
+SOLVER_BOUND_WARN = 1e-2      # a stagnated solve whose subspace-angle bound is above this is reported to the user
+
+
+def check_solver_outcome(info, config):
+    """The reference's svds raises ArpackNoConvergence when ARPACK gives up; here a solve that hit max_iters, or stopped on
+    the stagnation rules with a loose angle bound, still returns its embedding but never silently: a RuntimeWarning, or a
+    RuntimeError under the additive config key "solver_strict"."""
+    msg = None
+    if info["status"] == N.ENOTCONV or info["converged"] == 0:
+        msg = (f"UASE solver stopped at max_iters = {info['iterations']} operator applications without converging "
+               f"(subspace-angle bound {info['angle_bound']:.2e}); embeddings and rankings may be inaccurate")
+    elif info["converged"] == 2 and not (info["angle_bound"] <= SOLVER_BOUND_WARN):
+        msg = (f"UASE solver stopped because the residuals stagnated (fp32 floor) with subspace-angle bound "
+               f"{info['angle_bound']:.2e} > {SOLVER_BOUND_WARN:g}: some swept dimension cuts a cluster of singular values")
+    if msg:
+        if config.get("solver_strict"):
+            raise RuntimeError(msg)
+        warnings.warn(msg, RuntimeWarning, stacklevel=3)
 
 
 class N2V2R:
@@ -65,9 +86,14 @@ class N2V2R:
         if self.config["save_dir"]:
             self.save_dir = os.path.join(self.config["save_dir"], now)
             print(self.save_dir)
-            os.makedirs(self.save_dir)
-            with open(os.path.join(self.save_dir, "config.json"), 'w', encoding="utf-8") as f:
-                json.dump(self.config, f)
+            if self._writes_files():
+                os.makedirs(self.save_dir)          # raises when two runs start in the same second, like the reference
+                with open(os.path.join(self.save_dir, "config.json"), 'w', encoding="utf-8") as f:
+                    json.dump(self.config, f)
+
+    def _writes_files(self):
+        """Under torch.distributed (layer_sharded / seed_sharded runs) every rank holds the full tables; rank 0 writes them."""
+        return not dist.is_distributed() or torch.distributed.get_rank() == 0
 
     # ---- device residency -----------------------------------------------------------------
     def _device_layers(self):
@@ -77,7 +103,8 @@ class N2V2R:
             planes = self.config.get("storage_planes")
             if arrays and all(a.dtype == np.float32 and a.ndim == 2 and a.shape == arrays[0].shape for a in arrays):
                 # H2D of layer t+1 overlaps the load pass of layer t; large sparse layers cross PCIe packed (K0c)
-                built = iter(D.layers_from_host(arrays, n_planes=planes, transfer=self.config.get("host_transfer", "auto")))
+                built = iter(D.layers_from_host(arrays, n_planes=planes, transfer=self.config.get("host_transfer", "auto"),
+                                                storage=self.config.get("layer_storage", "auto")))
                 self.transfer_stats = D.layers_from_host.last_stats
                 self._layers = [g if a is None else next(built) for g, a in zip(self.graphs, host)]
                 return self._layers
@@ -89,16 +116,18 @@ class N2V2R:
                     x = D.to_device(a)
                     if x.dtype != torch.float32:        # the reference hands fp32 to the SVD (preprocessing_utils.py:141)
                         x = x.to(torch.float32)
-                    layers.append(D.make_layer(x, n_planes=planes))
+                    layers.append(D.make_layer(x, n_planes=planes, storage=self.config.get("layer_storage", "auto")))
             self._layers = layers
         return self._layers
 
     def _global_layers(self, layers):
         """(total number of layers over all ranks, index of this rank's first layer)."""
-        counts = torch.tensor([len(layers)], device=layers[0].planes.device)
+        counts = torch.tensor([len(layers)], device=N.require_gpu())
         allc = [torch.zeros_like(counts) for _ in range(torch.distributed.get_world_size())]
         torch.distributed.all_gather(allc, counts)
         vals = [int(c.item()) for c in allc]
+        if min(vals) == 0:
+            raise ValueError(f"layer_sharded: every rank needs at least one layer (layers per rank: {vals})")
         return sum(vals), sum(vals[:torch.distributed.get_rank()])
 
     def _solver_seed(self):
@@ -126,6 +155,7 @@ class N2V2R:
                                      max_iters=int(self.config.get("solver_max_iters", 400)),
                                      seed=self._solver_seed(), check_dims=self.embed_dimensions,
                                      T_global=T_global, layer_offset=offset)
+        check_solver_outcome(info, self.config)
         if sharded:
             emb = dist.gather_layers(emb, T_global)
         self.num_graphs = T_global
@@ -166,7 +196,7 @@ class N2V2R:
         toc_n2v2r = time.time()
         if self.config["verbose"] >= 0:
             print(f"""n2v2r computed {num_rankings} rankings for {len(self.pairwise_ranks)} comparison(s) in {round(toc_n2v2r - tic_n2v2r, 2)} seconds""")
-        if self.config["save_dir"]:
+        if self.config["save_dir"] and self._writes_files():
             for key, rank in self.pairwise_ranks.items():
                 rank.to_csv(os.path.join(self.save_dir, key + ".tsv"), sep='\t', index=True)
         return self.pairwise_ranks
@@ -202,14 +232,28 @@ class N2V2R:
             exec_time_agg = round(time.time() - start_time, 2)
             if self.config["verbose"] == 1:
                 print(f"\tFinished aggregation in {exec_time_agg} seconds")
-            if self.config["save_dir"]:
+            if self.config["save_dir"] and self._writes_files():
                 for k, rank in self.pairwise_aggregate_ranks.items():
                     rank.to_csv(os.path.join(self.save_dir, k + "_agg.tsv"), sep='\t', index=True)
         else:
             raise ValueError("No n2v2r embeddings found")
         return self.pairwise_aggregate_ranks
 
-    # ---- signed ranks: model.py:203-280 (host-side select over the score tables) -------------
+    # ---- signed ranks: model.py:203-280; the sign transfer runs on the device (K11b) -----------
+    def _signed_table(self, table, prior, dev):
+        """signed_transform_single (model_utils.py:7-19) for every column of `table` at once: rows whose node is missing
+        from the prior are dropped, the rest keep their score where the prior is > 0 and are negated otherwise."""
+        keep = table.index.isin(prior.index)
+        kept = table.index[keep]
+        p = torch.from_numpy(np.ascontiguousarray(prior.loc[kept].to_numpy(dtype=np.float64))).to(dev)
+        vals = table.to_numpy()
+        is_int = np.issubdtype(vals.dtype, np.integer)
+        block = np.ascontiguousarray(vals[keep].T.astype(np.int64 if is_int else np.float64))
+        if block.shape[1] == 0:
+            return kept, block.T
+        out = D.signed_scores(torch.from_numpy(block).to(dev), p)
+        return kept, D.to_host(out).T
+
     def signed_ranks_transform(self, prior_signed_ranks: pd.Series = None):
         if prior_signed_ranks is None:
             if self.prior_singed_ranks:
@@ -220,28 +264,24 @@ class N2V2R:
         if self.pairwise_ranks:
             print("\nSigned ranks transformation ...")
             start_time = time.time()
+            dev = N.require_gpu()
             signed, signed_agg = {}, {}
             for index, comparison_key in enumerate(self.pairwise_ranks):
                 table = self.pairwise_ranks[comparison_key]
                 prior = prior_signed_ranks[index]
-                cols = {}
-                last = None
-                for name in table.columns:
-                    last = signed_transform_single(table[name], prior)
-                    cols[name] = last.values
-                frame = pd.DataFrame(cols)
-                frame.index = last.index
-                signed[comparison_key] = frame
+                kept, vals = self._signed_table(table, prior, dev)
+                signed[comparison_key] = pd.DataFrame(vals, index=list(kept), columns=table.columns, copy=False)
                 if self.pairwise_aggregate_ranks:
-                    s = signed_transform_single(self.pairwise_aggregate_ranks[comparison_key].iloc[:, 0], prior)
-                    signed_agg[comparison_key] = pd.DataFrame(s.values, index=s.index, columns=["signed_agg_ranks"])
+                    agg = self.pairwise_aggregate_ranks[comparison_key].iloc[:, [0]]
+                    kept_a, vals_a = self._signed_table(agg, prior, dev)
+                    signed_agg[comparison_key] = pd.DataFrame(vals_a[:, 0], index=list(kept_a), columns=["signed_agg_ranks"])
         self.pairwise_signed_ranks = signed
         if self.pairwise_aggregate_ranks:
             self.pairwise_signed_aggregate_ranks = signed_agg
         exec_time_signed = round(time.time() - start_time, 2)
         if self.config["verbose"] == 1:
             print(f"\tFinished signed transformation in {exec_time_signed} seconds")
-        if self.config["save_dir"]:
+        if self.config["save_dir"] and self._writes_files():
             for k in self.pairwise_signed_ranks:
                 self.pairwise_signed_ranks[k].to_csv(os.path.join(self.save_dir, k + "_signed.tsv"), sep='\t', index=True)
             if self.pairwise_aggregate_ranks:
@@ -268,7 +308,7 @@ class N2V2R:
             ranking.index = self.node_names
             pairwise[str(i)] = ranking
         self.prior_singed_ranks = [v.iloc[:, 0] for k, v in pairwise.items()]
-        if self.config["save_dir"]:
+        if self.config["save_dir"] and self._writes_files():
             for k, rank in pairwise.items():
                 rank.to_csv(os.path.join(self.save_dir, k + "_degDif.tsv"), sep='\t', index=True)
         return pairwise

@@ -27,7 +27,7 @@ import torch
 from . import _native as N
 from . import device as D
 from . import dist
-from .model import N2V2R
+from .model import N2V2R, check_solver_outcome
 
 
 class StabilityRun:
@@ -83,6 +83,7 @@ class StabilityRun:
                                      max_iters=int(cfg.get("solver_max_iters", 400)), seed=seed,
                                      check_dims=m.embed_dimensions)
             info["seed"] = seed
+            check_solver_outcome(info, cfg)
             self.solver_infos.append(info)
             local.append(D.distances(emb, dims, mets, strategy))          # (C, cols, n)
         n_comp = len(layers) if strategy == N.ONE_VS_REST else len(layers) - 1

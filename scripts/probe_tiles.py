@@ -1,0 +1,53 @@
+"""Developer probe: one C3-sized layer stored as dense bf16 planes and as compressed tiles, both products timed with CUDA events
+(layer_apply = split + MMA kernel + reduce), bit-compared at a common K chunk.  Needs a GPU.
+    python scripts/probe_tiles.py [n] [l] [keep_percent] [reps] [--only-tiles]"""
+import json, os, sys, time
+import numpy as np, torch
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from node2vec2rank_b200 import device as D, _native as N
+from node2vec2rank_b200.synthetic import block_matrices
+dev = N.require_gpu()
+args = [a for a in sys.argv[1:] if not a.startswith("--")]
+n = int(args[0]) if len(args) > 0 else 50000
+l = int(args[1]) if len(args) > 1 else 48
+keep = float(args[2]) if len(args) > 2 else 10.0
+reps = int(args[3]) if len(args) > 3 else 20
+only_tiles = "--only-tiles" in sys.argv
+Bs, _ = block_matrices(32, 2, seed=1)
+raw = D.sbm_generate(n, 32, Bs[0], seed=1, layer=0, weighted=True)
+t0 = time.perf_counter()
+Lt, f32 = D.preprocess_to_layer(raw, top_percent_keep=keep, want_f32=True, storage="tiles")
+torch.cuda.synchronize()
+t_tiles = time.perf_counter() - t0
+del raw
+out = {"n": n, "l": l, "keep": keep, "planes": Lt.n_planes, "tile_rows": Lt.tile_rows, "entries": int(Lt.entries.shape[0]),
+       "density": float(Lt.entries.shape[0]) / n / n, "tiles_bytes": Lt.nbytes, "build_tiles_s": t_tiles}
+x = torch.randn((n, l), device=dev)
+ws = torch.empty(N.load().n2v2r_apply_workspace_bytes(n, l, 0), dtype=torch.uint8, device=dev)
+
+
+def timed(layer, k_chunk=0):
+    for _ in range(3):
+        y = D.layer_apply(layer, x, ws=ws if k_chunk == 0 else None, k_chunk=k_chunk)
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(reps):
+        y = D.layer_apply(layer, x, ws=ws if k_chunk == 0 else None, k_chunk=k_chunk)
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) / reps, y
+
+
+ms_t, y_t = timed(Lt)
+out["tiles_ms"] = ms_t
+if not only_tiles:
+    Lp = D.make_layer(f32, storage="planes")
+    del f32
+    ms_p, y_p = timed(Lp)
+    out["planes_ms"] = ms_p
+    out["speedup"] = ms_p / ms_t
+    out["max_rel_diff_default_splits"] = float(((y_t - y_p).abs().max() / y_p.abs().max()).item())
+    _, a = timed(Lt, 4096)
+    _, b = timed(Lp, 4096)
+    out["bit_identical_k4096"] = bool(torch.equal(a.view(torch.int32), b.view(torch.int32)))
+print(json.dumps(out), flush=True)

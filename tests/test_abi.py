@@ -7,6 +7,7 @@ import subprocess
 import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "n2v2r_b200.h")
 
 
 def _declared():
@@ -23,14 +24,29 @@ def test_header_symbols_exported(lib):
         assert hasattr(lib, name), f"{name} declared in include/n2v2r_b200.h but not exported"
         assert name in _native.SIGNATURES, f"{name} has no ctypes signature"
     assert sorted(_native.SIGNATURES) == names
-    assert lib.n2v2r_abi_version() == 1
+    assert lib.n2v2r_abi_version() == 2
 
 
-def test_struct_layout_matches_header(lib):
+def test_struct_layout_matches_header(lib, tmp_path):
+    """sizeof / offsetof of every struct of the header, printed by a C program compiled from the header itself, against
+    the ctypes mirrors in _native.py."""
     from node2vec2rank_b200 import _native as N
-    assert ctypes.sizeof(N.Layer) == 32
-    assert N.UaseParams.tol.offset % 8 == 0 and N.UaseStats.stream_ms.offset == 24
-    assert ctypes.sizeof(N.UaseStats) == 24 + 8 * 2 + 8 + 8 * 3 + 8 * 96 * 2
+    structs = {"n2v2r_layer_t": N.Layer, "n2v2r_uase_params_t": N.UaseParams, "n2v2r_uase_stats_t": N.UaseStats}
+    lines = ['#include <stdio.h>', '#include <stddef.h>', f'#include "{HEADER}"', 'int main(void) {']
+    for cname, cls in structs.items():
+        lines.append(f'  printf("{cname} %zu\\n", sizeof({cname}));')
+        for fname, _ in cls._fields_:
+            lines.append(f'  printf("{cname}.{fname} %zu\\n", offsetof({cname}, {fname}));')
+    lines += ['  return 0;', '}']
+    src = tmp_path / "layout.c"
+    src.write_text("\n".join(lines))
+    exe = tmp_path / "layout"
+    subprocess.run(["gcc", "-o", str(exe), str(src)], check=True)
+    got = dict(line.split() for line in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.splitlines())
+    for cname, cls in structs.items():
+        assert int(got[cname]) == ctypes.sizeof(cls), cname
+        for fname, _ in cls._fields_:
+            assert int(got[f"{cname}.{fname}"]) == getattr(cls, fname).offset, (cname, fname)
 
 
 def test_sass_has_tcgen05_and_tma(lib):

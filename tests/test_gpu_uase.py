@@ -217,7 +217,7 @@ def test_full_size_c3_properties(gpu):
         raw = D.sbm_generate(n, K, Bs[t], seed=1, layer=t, weighted=True)
         layers.append(D.preprocess_to_layer(raw, top_percent_keep=10)[0])
         del raw
-    assert all(L.n_planes == 2 and L.symmetric for L in layers)
+    assert all(L.n_planes == 2 and L.symmetric and L.storage == "tiles" for L in layers)     # 2.6 % dense: compressed tiles
     dims = list(range(4, 25, 2))
     emb, sigma, left, info = D.uase(layers, k, l=l, seed=42, check_dims=dims, want_left=True)
     assert info["converged"] and info["iterations"] <= 40, info
@@ -225,13 +225,24 @@ def test_full_size_c3_properties(gpu):
     G = torch.einsum("tnd,tne->de", emb.double(), emb.double()).cpu().numpy()
     assert np.allclose(np.diag(G), sigma, rtol=1e-5)
     assert np.abs(G - np.diag(np.diag(G))).max() <= 1e-5 * sigma[0]
+    # a second, independent solve (other start block, wider block): the two subspaces agree to the 1e-4 tolerance at every d
+    emb2, sigma2, _, info2 = D.uase(layers, k, l=80, seed=1000045, check_dims=dims)
+    assert np.allclose(sigma, sigma2, rtol=2e-6)
+    angles = D.subspace_sin_angles(emb, emb2, dims)
+    assert max(angles.values()) <= 1e-4, (angles, info["angle_bounds"], info2["angle_bounds"])
+    del emb2
+    # residuals with the independent SIMT product on dense planes rebuilt from the tiles (checks to_dense as well)
     U = (left.double() / torch.from_numpy(np.sqrt(sigma)).to(gpu)).float()
     pad = torch.zeros((n, l), dtype=torch.float32, device=gpu)
     pad[:, :k] = U
     MU = torch.zeros_like(pad)
     for L in layers:
-        z = D.layer_apply(L, pad, transpose=True, algo=N.ALGO_SIMT)
-        MU += D.layer_apply(L, z, transpose=False, algo=N.ALGO_SIMT)
+        dense = L.to_dense()
+        Lp = D.make_layer(dense, storage="planes", n_planes=2, check_symmetry=False)
+        del dense
+        z = D.layer_apply(Lp, pad, transpose=True, algo=N.ALGO_SIMT)
+        MU += D.layer_apply(Lp, z, transpose=False, algo=N.ALGO_SIMT)
+        del Lp
     lam = torch.from_numpy(sigma ** 2).to(gpu)
     r = (MU[:, :k].double() - U.double() * lam).norm(dim=0) / lam
     assert float(r.max()) <= 2e-5, r
