@@ -295,6 +295,18 @@ int n2v2r_scatter_edges(void* stream, const int32_t* d_u, const int32_t* d_v, co
                         void* d_out, int dtype, int64_t n, int64_t ld);
 
 /* ------------------------------------------------------------------------------------
+ * K0d  device side of match_networks for adjacency files.  Replaces the `.loc[common_rows, common_cols]` reindex
+ * (preprocessing_utils.py:291-306) and the optional `.T` (dataloader.py:103) of DataLoader.__load_graph's CSV branch
+ * (dataloader.py:86-91): the file is parsed in row chunks on the host, each chunk goes through pinned memory into a
+ * float64 device matrix in FILE order, and this kernel writes the matrix of the common nodes in their final order:
+ * out[i][j] = in[row_idx[i]][col_idx[j]], or with transpose != 0 out[i][j] = in[col_idx[j]][row_idx[i]]
+ * (row_idx then indexes the file's columns and col_idx its rows).  Indices must lie inside `in`.
+ * ---------------------------------------------------------------------------------- */
+int n2v2r_gather_submatrix(void* stream, const double* d_in, int64_t in_rows, int64_t in_cols, int64_t ld_in,
+                           const int32_t* d_row_idx, const int32_t* d_col_idx, int64_t out_rows, int64_t out_cols,
+                           int transpose, double* d_out, int64_t ld_out);
+
+/* ------------------------------------------------------------------------------------
  * K0c  sparse host->device transfer of a dense fp32 layer.  The reference converts every
  * dense float32 graph to CSC on the host before the SVD (N2V2R.__fit, model.py:51-55); here
  * the host side of that conversion only serves the PCIe copy: n2v2r_host_pack_nonzeros

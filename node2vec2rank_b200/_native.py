@@ -93,6 +93,7 @@ SIGNATURES = {
     "n2v2r_signed_scores": (_i, [_vp, _vp, _i, _i64, _i, _vp, _vp]),
     "n2v2r_ndcg": (_i, [_vp, _vp, _i64, _i64, _vp, _i64, _vp, _vp]),
     "n2v2r_scatter_edges": (_i, [_vp, _vp, _vp, _vp, _i64, _vp, _i, _i64, _i64]),
+    "n2v2r_gather_submatrix": (_i, [_vp, _vp, _i64, _i64, _i64, _vp, _vp, _i64, _i64, _i, _vp, _i64]),
     "n2v2r_host_pack_nonzeros": (_i, [_vp, _i64, _i64, _i64, _vp, _vp, _i64, _vp, _i, _vp]),
     "n2v2r_unpack_nonzeros": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _vp, _i64]),
 }

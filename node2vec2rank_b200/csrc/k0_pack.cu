@@ -70,9 +70,56 @@ __global__ void __launch_bounds__(kUnpackThreads) unpack_rows_kernel(const uint3
   }
 }
 
+// ---- K0d: reindex a parsed adjacency block into the common node order (device side of match_networks) ----
+// out[i][j] = in[ri[i]][ci[j]]  (transpose: out[i][j] = in[ci[j]][ri[i]], i.e. graph_pd.T then .loc[rows, cols]).
+// 32 x 32 tiles through shared memory so that the transposed read stays coalesced along rows of `in`.
+__global__ void __launch_bounds__(256) gather_submatrix_kernel(const double* __restrict__ in, int64_t ld_in,
+                                                               const int32_t* __restrict__ ri, const int32_t* __restrict__ ci,
+                                                               int64_t out_rows, int64_t out_cols, int transpose,
+                                                               double* __restrict__ out, int64_t ld_out) {
+  __shared__ double t[32][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int64_t i0 = (int64_t)blockIdx.y * 32, j0 = (int64_t)blockIdx.x * 32;
+  if (!transpose) {
+    const int64_t j = j0 + tx;
+    const int64_t sc = j < out_cols ? ci[j] : -1;
+    for (int r = ty; r < 32; r += 8) {
+      const int64_t i = i0 + r;
+      if (i < out_rows && sc >= 0) out[i * ld_out + j] = in[(int64_t)ri[i] * ld_in + sc];
+    }
+    return;
+  }
+  // transposed: read rows ci[j] of `in` along i (columns ri[i]), write rows i of `out` along j
+  const int64_t ii = i0 + tx;
+  const int64_t scol = ii < out_rows ? ri[ii] : -1;
+  for (int r = ty; r < 32; r += 8) {
+    const int64_t j = j0 + r;
+    t[r][tx] = (j < out_cols && scol >= 0) ? in[(int64_t)ci[j] * ld_in + scol] : 0.0;     // t[j_local][i_local]
+  }
+  __syncthreads();
+  for (int r = ty; r < 32; r += 8) {
+    const int64_t i = i0 + r, j = j0 + tx;
+    if (i < out_rows && j < out_cols) out[i * ld_out + j] = t[tx][r];
+  }
+}
+
 }  // namespace n2v2r
 
 using namespace n2v2r;
+
+extern "C" int n2v2r_gather_submatrix(void* stream, const double* d_in, int64_t in_rows, int64_t in_cols, int64_t ld_in,
+                                      const int32_t* d_row_idx, const int32_t* d_col_idx, int64_t out_rows, int64_t out_cols,
+                                      int transpose, double* d_out, int64_t ld_out) {
+  N2V2R_REQUIRE(d_in && d_out && d_row_idx && d_col_idx, "gather_submatrix: null pointer");
+  N2V2R_REQUIRE(in_rows > 0 && in_cols > 0 && ld_in >= in_cols && out_rows >= 0 && out_cols >= 0 && ld_out >= out_cols,
+                "gather_submatrix: bad shape");
+  if (out_rows == 0 || out_cols == 0) return N2V2R_OK;
+  dim3 grid((unsigned)((out_cols + 31) / 32), (unsigned)((out_rows + 31) / 32));
+  gather_submatrix_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(d_in, ld_in, d_row_idx, d_col_idx, out_rows, out_cols, transpose,
+                                                                 d_out, ld_out);
+  N2V2R_CHECK_LAUNCH();
+  return N2V2R_OK;
+}
 
 extern "C" int n2v2r_unpack_nonzeros(void* stream, const uint32_t* d_bitmap, const void* d_values, const int64_t* d_row_start,
                                      int64_t rows, int64_t cols, void* d_out, int64_t ld) {

@@ -6,6 +6,9 @@ Additive config keys (all optional, defaults keep the reference behaviour):
       objects (bf16 planes) instead of float32 ndarrays; N2V2R accepts both.
   storage_planes (int 1..3 | None): bf16 planes per weighted layer (None = as many as needed
       to be exact; binarised layers always use one).
+  csv_parser ("device" | "pandas", default "device"): adjacency files are parsed in row chunks through pinned memory into
+      device matrices and reindexed to the common nodes on the device (K0d); "pandas" keeps the reference's whole-file
+      pd.read_csv + host reindex.  .h5 files always take the pandas path.
   edge_list_parser ("device" | "networkx", default "device"): edge lists are parsed by pandas and scattered into the
       dense matrix on the device (K0b); "networkx" keeps the reference's nx.read_weighted_edgelist path.
 """
@@ -39,6 +42,9 @@ class DataLoader():
         print('Loading graphs in memory ...')
         if self.config["is_edge_list"] and self.config.get("edge_list_parser", "device") == "device":
             row_nodes = col_nodes = self.__load_edge_lists_device()
+        elif (not self.config["is_edge_list"] and self.config.get("csv_parser", "device") == "device"
+              and all(fn.split(".")[-1] != "h5" for fn in self.__graph_filenames)):
+            row_nodes, col_nodes = self.__load_adjacency_device()
         else:
             for i, graph_filename in enumerate(self.__graph_filenames):
                 self.graphs.append(self.__load_graph(graph_filename=graph_filename, graph_index=i))
@@ -74,11 +80,17 @@ class DataLoader():
 
         kwargs = dict(binarize=cfg['binarize'], threshold=cfg['threshold'], absolute=cfg['absolute'],
                       top_percent_keep=cfg['top_percent_keep'], project_unipartite_on=cfg['project_unipartite_on'])
-        if cfg.get("device_resident", False):
-            self.graphs = [network_transform_device(g, storage_planes=cfg.get("storage_planes"), **kwargs)[0]
-                           for g in self.graphs]
-        else:
-            self.graphs = [network_transform(g, **kwargs) for g in self.graphs]
+        pending, self.graphs = self.graphs, []
+        while pending:                      # one graph at a time: device-side inputs are built, transformed and released in turn
+            g = pending.pop(0)
+            if callable(g):
+                g = g()
+            if cfg.get("device_resident", False):
+                self.graphs.append(network_transform_device(g, storage_planes=cfg.get("storage_planes"),
+                                                            storage=cfg.get("layer_storage", "auto"), **kwargs)[0])
+            else:
+                self.graphs.append(network_transform(g, **kwargs))
+            del g
 
         toc_loading = time.time()
         print(f"""Finished loading in {round(toc_loading - tic_loading, 2)} seconds \n""")
@@ -119,10 +131,70 @@ class DataLoader():
         common = set.intersection(*[set(p[0].to_list()) for p in parsed])
         final = pd.Index([x for x in parsed[0][0].to_list() if x in common])
         n = len(final)
+        if n == 0:
+            raise ValueError("the graphs have no nodes in common")
         for nodes, lo, hi, w in parsed:
             pos = final.get_indexer(nodes).astype(np.int32)               # -1: node not shared by every graph
-            self.graphs.append(D.dense_from_edges(pos[lo], pos[hi], w, n) if n else np.zeros((0, 0)))
+            # a thunk: the dense float64 matrix of a graph exists only while the transform loop works on it
+            self.graphs.append(lambda pos=pos, lo=lo, hi=hi, w=w: D.dense_from_edges(pos[lo], pos[hi], w, n))
         return final.to_numpy()
+
+    def __load_adjacency_device(self):
+        """Adjacency files -> float64 device matrices restricted to the common nodes, in the order of the first graph.
+
+        Replaces pd.read_csv (whole file, float64 DataFrame) + optional .T + match_networks' .loc reindex
+        (dataloader.py:86-91, :103, preprocessing_utils.py:291-306): device.csv_to_device parses row chunks through pinned
+        staging buffers into a device matrix in file order, K0d (device.gather_submatrix) picks / reorders / transposes the
+        common rows and columns on the device.  The entries of self.graphs are thunks: each graph is reindexed (and, when the
+        files are too large to sit in HBM together, parsed) only when the transform loop asks for it, so at most one
+        float64 intermediate is alive besides the outputs.  Duplicate labels fall back to the pandas path (.loc semantics)."""
+        import torch
+        from . import device as D
+        sep, transpose = self.config["separator"], bool(self.config["transpose"])
+        paths = [os.path.join(self.config["data_dir"], fn) for fn in self.__graph_filenames]
+        sizes = [os.path.getsize(p) for p in paths]
+        free = torch.cuda.mem_get_info()[0] if torch.cuda.is_available() else 0
+        keep_all = 4.0 * sum(sizes) < 0.4 * free       # a float64 cell is 8 bytes, its text rarely under 2: all files fit together
+        parsed = []
+        for i, path in enumerate(paths):
+            if keep_all:
+                x, rows, cols = D.csv_to_device(path, sep)
+            else:                                      # labels only now (header + first column); the cells are parsed later
+                x = None
+                cols = pd.read_csv(path, index_col=0, header=0, sep=sep, nrows=0).columns
+                rows = pd.Index(pd.read_csv(path, usecols=[0], header=0, sep=sep).iloc[:, 0])
+            if transpose:
+                rows, cols = cols, rows
+            if not (rows.is_unique and cols.is_unique):
+                del parsed, x
+                self.graphs = []
+                for j, fn in enumerate(self.__graph_filenames):
+                    self.graphs.append(self.__load_graph(graph_filename=fn, graph_index=j))
+                self.graphs = match_networks(self.graphs)
+                return self.graphs[0].index.to_numpy(), self.graphs[0].columns.to_numpy()
+            print(f"""\tThere are {len(rows)} row nodes and {len(cols)} column nodes in graph {i+1}""")
+            parsed.append([x, rows, cols, path])
+        common_cols = set.intersection(*[set(p[2].to_list()) for p in parsed])
+        common_rows = set.intersection(*[set(p[1].to_list()) for p in parsed])
+        final_rows = parsed[0][1][parsed[0][1].isin(common_rows)]
+        final_cols = parsed[0][2][parsed[0][2].isin(common_cols)]
+        if len(final_rows) == 0 or len(final_cols) == 0:
+            raise ValueError("the graphs have no nodes in common")
+
+        def thunk(entry):
+            def build():
+                x, rows, cols, path = entry
+                if x is None:
+                    x = D.csv_to_device(path, sep)[0]
+                entry[0] = None                        # the file-order matrix is released once the graph is built
+                ri, ci = rows.get_indexer(final_rows), cols.get_indexer(final_cols)
+                same = (not transpose and len(ri) == x.shape[0] and len(ci) == x.shape[1]
+                        and np.array_equal(ri, np.arange(len(ri))) and np.array_equal(ci, np.arange(len(ci))))
+                return x.contiguous() if same else D.gather_submatrix(x, ri, ci, transpose=transpose)
+            return build
+
+        self.graphs = [thunk(p) for p in parsed]
+        return final_rows.to_numpy(), final_cols.to_numpy()
 
     def __load_graph(self, graph_filename, graph_index):
         extension_type = graph_filename.split(".")[-1]

@@ -139,6 +139,85 @@ def dense_from_edges(iu, iv, w, n, dtype=torch.float64):
     return out
 
 
+CSV_CHUNK_ENTRIES = 16_000_000        # rows are parsed and copied in chunks of about this many cells (128 MB of float64)
+
+
+def csv_to_device(path, sep, chunk_entries=None):
+    """Adjacency file (first column = row labels, first line = column labels; what pd.read_csv(index_col=0, header=0)
+    reads, dataloader.py:86-91) -> (float64 (rows, cols) device matrix in FILE order, row labels, column labels).
+
+    The file is parsed by pandas' C reader in chunks of rows; every chunk is copied into one of two pinned staging
+    buffers and sent to the device on a copy stream while the next chunk is being parsed: no full float64 DataFrame on
+    the host, no pageable copy.  Labels are exactly what pandas infers for the whole file."""
+    import pandas as pd
+    dev = _dev()
+    cols = pd.read_csv(path, index_col=0, header=0, sep=sep, nrows=0).columns
+    c = len(cols)
+    with open(path, "rb") as f:                       # upper bound of the number of data rows: newlines after the header
+        lines = 0
+        while True:
+            block = f.read(1 << 24)
+            if not block:
+                break
+            lines += block.count(b"\n")
+            last = block[-1:]
+        if lines and last != b"\n":
+            lines += 1
+    cap = max(lines - 1, 0)
+    out = torch.empty((max(cap, 1), max(c, 1)), dtype=torch.float64, device=dev)
+    chunk_rows = max(1, (chunk_entries or CSV_CHUNK_ENTRIES) // max(c, 1))
+    stage = [torch.empty((chunk_rows, max(c, 1)), dtype=torch.float64, pin_memory=True) for _ in range(2)]
+    sent = [None, None]
+    copy = torch.cuda.Stream(dev)
+    copy.wait_stream(torch.cuda.current_stream(dev))
+    labels, r0, k = [], 0, 0
+    for chunk in pd.read_csv(path, index_col=0, header=0, sep=sep, chunksize=chunk_rows):
+        vals = chunk.to_numpy(dtype=np.float64)        # ValueError on non-numeric cells
+        r = vals.shape[0]
+        if r0 + r > cap:
+            raise ValueError(f"{path}: more data rows than lines")
+        slot = k % 2
+        if sent[slot] is not None:
+            sent[slot].synchronize()                    # the previous copy out of this staging buffer has finished
+        stage[slot][:r].copy_(torch.from_numpy(vals))
+        with torch.cuda.stream(copy):
+            out[r0:r0 + r].copy_(stage[slot][:r], non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(copy)
+        sent[slot] = ev
+        labels.append(chunk.index)
+        r0 += r
+        k += 1
+    torch.cuda.current_stream(dev).wait_stream(copy)
+    copy.synchronize()                                  # the staging buffers go out of scope
+    if not labels:
+        rows = pd.Index([])
+    elif len({str(ix.dtype) for ix in labels}) == 1 and labels[0].dtype != object:
+        rows = labels[0].append(labels[1:]) if len(labels) > 1 else labels[0]
+    elif len(labels) == 1:
+        rows = labels[0]
+    else:            # pandas infers the label type per chunk; mixed chunks -> what it infers for the whole first column
+        rows = pd.Index(pd.read_csv(path, usecols=[0], header=0, sep=sep).iloc[:, 0])
+    return out[:r0, :c], rows, cols
+
+
+def gather_submatrix(x: torch.Tensor, row_idx, col_idx, transpose=False):
+    """K0d: the (len(row_idx), len(col_idx)) float64 device matrix out[i][j] = x[row_idx[i]][col_idx[j]]
+    (transpose: x[col_idx[j]][row_idx[i]]) -- match_networks' reindex (and dataloader.py:103's .T) on the device."""
+    lib = N.load()
+    if x.dtype != torch.float64 or x.dim() != 2:
+        raise TypeError("gather_submatrix expects a float64 matrix")
+    ri = torch.as_tensor(np.ascontiguousarray(row_idx, dtype=np.int32)).to(x.device)
+    ci = torch.as_tensor(np.ascontiguousarray(col_idx, dtype=np.int32)).to(x.device)
+    lim_r, lim_c = (x.shape[1], x.shape[0]) if transpose else (x.shape[0], x.shape[1])
+    if ri.numel() and (int(ri.min()) < 0 or int(ri.max()) >= lim_r) or ci.numel() and (int(ci.min()) < 0 or int(ci.max()) >= lim_c):
+        raise IndexError("gather_submatrix: index outside the matrix")
+    out = torch.empty((ri.numel(), ci.numel()), dtype=torch.float64, device=x.device)
+    N.check(lib.n2v2r_gather_submatrix(N.stream_ptr(), N.ptr(x), x.shape[0], x.shape[1], x.stride(0), N.ptr(ri), N.ptr(ci),
+                                       ri.numel(), ci.numel(), int(bool(transpose)), N.ptr(out), max(ci.numel(), 1)))
+    return out
+
+
 def select_nonzero(x: torch.Tensor, frac: float, absolute=False, threshold=None):
     """K1a: (nnz, v_lo, v_hi, virtual_index) of the nonzeros of the (abs/thresholded) matrix."""
     lib = N.load()

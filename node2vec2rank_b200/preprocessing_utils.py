@@ -27,12 +27,12 @@ def bipartite_to_unipartite_projection(graph, project_unipartite_on="columns"):
 
 
 def network_transform_device(network, threshold=None, top_percent_keep=100, binarize=False, absolute=False,
-                             project_unipartite_on="columns", storage_planes=None, want_f32=False):
+                             project_unipartite_on="columns", storage_planes=None, want_f32=False, storage="auto"):
     """Device-resident variant: returns (DeviceLayer, fp32 device tensor | None)."""
     x = D.to_device(network)
     return D.preprocess_to_layer(x, threshold=threshold, top_percent_keep=top_percent_keep, binarize=binarize,
                                  absolute=absolute, project_unipartite_on=project_unipartite_on,
-                                 storage_planes=storage_planes, want_f32=want_f32)
+                                 storage_planes=storage_planes, want_f32=want_f32, storage=storage)
 
 
 def network_transform(network, threshold=None, top_percent_keep=100, binarize=False, absolute=False,
