@@ -475,11 +475,15 @@ def build_workload_layers(w, n, layer_ids, want_f32=False, storage="auto", graph
     return layers, f32s, events
 
 
-def hot_path(layers, w, l, seed=SOLVER_SEED, T_global=None, layer_offset=0, gather=None, dims=None, metrics=None):
+def hot_path(layers, w, l, seed=SOLVER_SEED, T_global=None, layer_offset=0, gather=None, dims=None, metrics=None, shard=None):
     """One step of the benchmark: UASE solve at k = max(dims) with the gap-aware stop at every swept d, distances for every
-    (d, metric), rank + Borda of all comparisons.  Returns (info, emb (T, n, k), scores (C, cols, n), bordas (C, n))."""
+    (d, metric), rank + Borda of all comparisons.  Returns (info, emb (T, n, k), scores (C, cols, n), bordas (C, n)).
+    shard = (rank, world, all_reduce): the (d, metric) columns of the sweep are split over the ranks (every rank holds all
+    embeddings after the gather), each rank scores and ranks its columns, and the Borda points are summed with one
+    all-reduce; `scores` then holds this rank's columns only."""
     from node2vec2rank_b200 import _native as N
     from node2vec2rank_b200 import device as D
+    from node2vec2rank_b200 import dist as ND
     dims = DIMS if dims is None else dims
     names, cdims, cmets = D.column_specs(dims, METRICS if metrics is None else metrics)
     emb, sigma, _, info = D.uase(layers, max(dims), l=l, tol=1e-5, max_iters=400, seed=seed, check_dims=dims,
@@ -487,19 +491,27 @@ def hot_path(layers, w, l, seed=SOLVER_SEED, T_global=None, layer_offset=0, gath
     info["sigma"] = sigma
     if gather is not None:
         emb = gather(emb)
+    if shard is not None and shard[1] > 1:
+        mine = ND.layer_partition(len(cdims), shard[1], shard[0])
+        cdims, cmets = cdims[mine.start:mine.stop], cmets[mine.start:mine.stop]
     scores = D.distances(emb, cdims, cmets, N.STRATEGIES[w["strategy"]])
-    bordas = D.rank_borda(scores)[0]                       # all comparisons in one launch
+    if scores.shape[1]:
+        bordas = D.rank_borda(scores)[0]                   # all comparisons in one launch
+    else:
+        bordas = scores.new_zeros((scores.shape[0], scores.shape[2]), dtype=__import__("torch").int64)
+    if shard is not None and shard[1] > 1:
+        shard[2](bordas)                                   # Borda points are additive over the columns
     return info, emb, scores, bordas
 
 
-def cross_solve_check(layers, w, l, emb, bordas, T_global, layer_offset, gather):
+def cross_solve_check(layers, w, l, emb, bordas, T_global, layer_offset, gather, shard=None):
     """UNTIMED parity evidence at full size: a second, independent solve (other start block, wider block l = 80) and the
     principal angle between the two embeddings' subspaces at every swept d (device.subspace_sin_angles), plus the agreement
     of the two Borda tables.  Two solves that share nothing but the layers agree to 1e-4 only if both are converged."""
     from node2vec2rank_b200 import device as D
     l2 = 80 if l != 80 else 64
     info2, emb2, _, bordas2 = hot_path(layers, w, l2, seed=SOLVER_SEED + 1000003, T_global=T_global, layer_offset=layer_offset,
-                                       gather=gather)
+                                       gather=gather, shard=shard)
     ang = D.subspace_sin_angles(emb, emb2, DIMS)
     a, b = bordas.double(), bordas2.double()
     a = a - a.mean(dim=1, keepdim=True)
@@ -551,9 +563,10 @@ def run_b200_arm(args):
     layers_gb = sum(L.nbytes for L in layers) * T / max(len(layers), 1) / 1e9
     offset = mine.start if len(mine) else 0
     gather = (lambda e: ND.gather_layers(e, T)) if world > 1 else None
+    shard = (rank, world, lambda t: tdist.all_reduce(t)) if world > 1 else None
 
     def step():
-        info, emb, scores, bordas = hot_path(layers, w, l, T_global=T, layer_offset=offset, gather=gather)
+        info, emb, scores, bordas = hot_path(layers, w, l, T_global=T, layer_offset=offset, gather=gather, shard=shard)
         launches = info["kernel_launches"] + 2
         return info, scores, bordas, launches, emb
 
@@ -580,7 +593,7 @@ def run_b200_arm(args):
     clocks = sampler.stop() if rank == 0 else None
     sweep_ms = reduce_max(float(np.mean([max(0.0, ms_step - i["total_ms"]) for i in infos])))      # step minus solve
     # ---- untimed parity evidence: independent second solve, subspace angle per swept d ----------------
-    cross = None if args.no_cross_check else cross_solve_check(layers, w, l, emb, bordas, T, offset, gather)
+    cross = None if args.no_cross_check else cross_solve_check(layers, w, l, emb, bordas, T, offset, gather, shard)
     del emb
 
     # ---- roofline of the dominant kernel (tcgen05 streaming product), measured live in the timed steps ----
@@ -693,7 +706,7 @@ def stream_roofline(env, infos, ms_step, steps, n, n_planes, l, workload, layers
         rows_pad = -(-n // L.tile_rows) * L.tile_rows
         n_pad = -(-n // 64) * 64
         flop = 2.0 * rows_pad * n_pad * l * terms
-        entry_bytes = float(np.mean([x.entries.shape[0] * 8 + x.tile_ptr.numel() * 4 for x in layers]))
+        entry_bytes = float(np.mean([x.n_entries * 8 + x.tile_ptr.numel() * 4 for x in layers]))
         alg_bytes = entry_bytes + 4.0 * l * 2.0 * n
         achieved = flop / avg_s / 1e12 if mma_n else 0.0
         roof = {"bound": "tensor", "achieved": achieved, "peak": env.tc_peak, "unit": "TFLOP/s", "frac": achieved / env.tc_peak,

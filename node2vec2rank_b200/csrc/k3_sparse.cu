@@ -25,6 +25,7 @@ namespace n2v2r {
 
 constexpr int kLandCap = 512;        // entries per landing slot (4 KB)
 constexpr int kUndoCap = 2048;       // positions remembered per A stage; a denser tile pair is cleared as a whole
+constexpr int kSortCap = 2048;        // tile lists up to this length are written in bank-interleaved order (builder)
 constexpr uint32_t kPosSkip = 0xFFFFu;   // padding entry (tile lists are padded to an even number of entries)
 
 // element offset of (row r, column c) inside one K-major SWIZZLE_128B plane of a (tile_rows x 64) bf16 tile
@@ -176,6 +177,9 @@ __global__ void __launch_bounds__(256) tiles_fill_kernel(const float* __restrict
   constexpr int RPW = ROWS / 8;                // source rows per warp
   constexpr int EPL = COLS / 32;               // elements per lane per source row
   __shared__ uint32_t wtot[8];
+  __shared__ uint32_t bank_cnt[32];
+  __shared__ uint2 stage[kSortCap];
+  __shared__ uint16_t srank[kSortCap];
   const int kb = blockIdx.x, rt = blockIdx.y;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int64_t src_r0 = TRANS ? (int64_t)kb * 64 : (int64_t)rt * TR;
@@ -193,14 +197,19 @@ __global__ void __launch_bounds__(256) tiles_fill_kernel(const float* __restrict
     }
   }
   if (lane == 0) wtot[warp] = mine;
+  if (threadIdx.x < 32) bank_cnt[threadIdx.x] = 0;
   __syncthreads();
   const size_t tile = (size_t)rt * n_kb + kb;
-  uint32_t base = tile_ptr[tile];
-  uint32_t total = 0;
+  const uint32_t tile_base = tile_ptr[tile];
+  uint32_t base = 0, total = 0;
   for (int w = 0; w < 8; ++w) {
     if (w < warp) base += wtot[w];
     total += wtot[w];
   }
+  // Lists of up to kSortCap entries are staged in shared memory and written in BANK-INTERLEAVED order: entry number j of
+  // shared-memory bank b goes to slot (j, b), so that the 32 lanes of a converter warp, which scatter 32 consecutive
+  // entries with one store instruction, hit 32 different banks (a random order costs ~6 conflict wavefronts per store).
+  const bool sorted = total <= (uint32_t)kSortCap;
   const uint32_t lt = (1u << lane) - 1u;
 #pragma unroll
   for (int j = 0; j < RPW; ++j) {
@@ -216,12 +225,29 @@ __global__ void __launch_bounds__(256) tiles_fill_kernel(const float* __restrict
         uint2 ent;
         ent.x = swz_pos(r, c) | ((uint32_t)__bfloat16_as_ushort(hi) << 16);
         ent.y = (uint32_t)__bfloat16_as_ushort(mid) | ((uint32_t)__bfloat16_as_ushort(lo) << 16);
-        entries[(size_t)base + __popc(b & lt)] = ent;
+        const uint32_t idx = base + __popc(b & lt);
+        if (sorted) stage[idx] = ent;
+        else entries[(size_t)tile_base + idx] = ent;
       }
       base += __popc(b);
     }
   }
-  if (threadIdx.x == 0 && (total & 1u)) entries[(size_t)tile_ptr[tile] + total] = make_uint2(kPosSkip, 0u);
+  if (sorted) {
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < total; i += 256) srank[i] = (uint16_t)atomicAdd(&bank_cnt[(stage[i].x >> 1) & 31u], 1u);
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < total; i += 256) {
+      const uint32_t bank = (stage[i].x >> 1) & 31u, rk = srank[i];
+      uint32_t slot = 0;
+      for (uint32_t bb = 0; bb < 32; ++bb) {
+        const uint32_t cb = bank_cnt[bb];
+        slot += cb < rk ? cb : rk;                                   // complete rounds before mine
+        slot += (bb < bank && cb > rk) ? 1u : 0u;                    // banks ahead of mine in my round
+      }
+      entries[(size_t)tile_base + slot] = stage[i];
+    }
+  }
+  if (threadIdx.x == 0 && (total & 1u)) entries[(size_t)tile_base + total] = make_uint2(kPosSkip, 0u);
 }
 
 // test / to_dense helper: out[(rt*TR + r) * ld + kb*64 + c] = p0 + p1 + p2 (out zero-filled by the caller)
@@ -656,7 +682,7 @@ extern "C" int n2v2r_tiles_fill(void* stream, const float* d_in, int64_t n, int6
 
 extern "C" int n2v2r_tiles_to_dense(void* stream, const uint32_t* d_tile_ptr, const void* d_entries, int64_t n, int tile_rows,
                                     float* d_out, int64_t ld_out) {
-  N2V2R_REQUIRE(d_tile_ptr && d_entries && d_out && n > 0 && ld_out >= n && (tile_rows == 128 || tile_rows == 256), "tiles_to_dense: bad arguments");
+  N2V2R_REQUIRE(d_tile_ptr && d_out && n > 0 && ld_out >= n && (tile_rows == 128 || tile_rows == 256), "tiles_to_dense: bad arguments");
   cudaStream_t s = (cudaStream_t)stream;
   const int n_kb = (int)(round_up(n, 64) / 64), n_rt = (int)((n + tile_rows - 1) / tile_rows);
   tiles_to_dense_kernel<<<dim3((unsigned)n_kb, (unsigned)n_rt), 256, 0, s>>>(d_tile_ptr, (const uint2*)d_entries, n, n_kb, tile_rows, d_out, ld_out);

