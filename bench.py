@@ -67,11 +67,13 @@ def parse_args():
     ap.add_argument("--block-width", type=int, default=48, help="solver block width l (default = device.default_block_width(24, n))")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer end-to-end leg (development only)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (development only)")
-    ap.add_argument("--layer-storage", default="auto", choices=["auto", "planes", "tiles"],
+    ap.add_argument("--layer-storage", default="auto", choices=["auto", "planes", "tiles", "e4m3"],
                     help="how preprocessed layers are held in HBM (device.make_layer): dense bf16 planes, or compressed tiles "
                          "expanded in shared memory for sparse layers; auto = the product default")
     ap.add_argument("--no-cross-check", action="store_true",
                     help="skip the untimed second solve (other seed, l = 80) whose subspace angle against the timed solve is reported")
+    ap.add_argument("--seed-batch", type=int, default=16,
+                    help="workload c5: solves that run concurrently and share every pass over a layer (1 = one after the other)")
     ap.add_argument("--cpu-ladder", default="2000,4000,8000",
                     help="--impl reference: node counts the reference path is timed at (all layers), ascending")
     ap.add_argument("--cpu-budget-s", type=float, default=420.0, help="--impl reference: wall-clock budget of the ladder")
@@ -721,12 +723,14 @@ def stream_roofline(env, infos, ms_step, steps, n, n_planes, l, workload, layers
                         "the dense tile MMA work, not HBM, bounds the launch"}
         key = f"{workload}_tiles_bytes_per_launch"
     else:
-        alg_bytes = float(n) * n * 2.0 * n_planes + 4.0 * l * 2.0 * n          # matrix once + skinny in + skinny out
+        e4m3 = bool(layers) and layers[0].storage == "e4m3"
+        per_entry = 1.0 if e4m3 else 2.0 * n_planes
+        alg_bytes = float(n) * n * per_entry + 4.0 * l * 2.0 * n               # matrix once + skinny in + skinny out
         achieved = alg_bytes / avg_s / 1e9 if mma_n else 0.0
         roof = {"bound": "hbm", "achieved": achieved, "peak": env.hbm_peak, "unit": "GB/s", "frac": achieved / env.hbm_peak,
-                "traffic": None, "kernel": "stream_mma_kernel", "peak_source": env.hbm_src,
+                "traffic": None, "kernel": "stream_mma8_kernel" if e4m3 else "stream_mma_kernel", "peak_source": env.hbm_src,
                 "algorithmic_bytes_per_launch": alg_bytes}
-        key = f"{workload}_bytes_per_launch"
+        key = f"{workload}_e4m3_bytes_per_launch" if e4m3 else f"{workload}_bytes_per_launch"
     roof.update(common)
     # ncu dram__bytes_read + write per launch, captured once per (workload, n, planes, l, storage): only quoted when it matches
     try:
@@ -757,7 +761,8 @@ def run_b200_c5(args, w):
     layers, host_graphs = [], []
     for t in range(T):
         raw = D.sbm_generate(n, K, Bs[t], seed=GRAPH_SEED, layer=t, weighted=w["weighted"])
-        layer, f32 = D.preprocess_to_layer(raw, top_percent_keep=w["keep"], binarize=w["binarize"], want_f32=not args.no_e2e)
+        layer, f32 = D.preprocess_to_layer(raw, top_percent_keep=w["keep"], binarize=w["binarize"], want_f32=not args.no_e2e,
+                                           storage=args.layer_storage)
         del raw
         if f32 is not None:
             h = torch.empty((n, n), dtype=torch.float32, pin_memory=True)
@@ -770,12 +775,23 @@ def run_b200_c5(args, w):
     names, cdims, cmets = D.column_specs(DIMS, METRICS)
     strategy = N.STRATEGIES[w["strategy"]]
 
+    group = max(1, min(16, args.seed_batch))
+    batchable = group > 1 and layers[0].storage == "planes"
+    batch_log = []
+
     def step():
         infos, local = [], []
-        for seed in mine:
-            emb, _, _, info = D.uase(layers, max(DIMS), l=l, tol=1e-5, max_iters=400, seed=seed, check_dims=DIMS)
-            infos.append(info)
-            local.append(D.distances(emb, cdims, cmets, strategy))
+        for g0 in range(0, len(mine), group if batchable else 1):
+            chunk = mine[g0:g0 + (group if batchable else 1)]
+            if batchable and len(chunk) > 1:         # concurrent solves sharing every pass over a layer (device.uase_batched)
+                solved, bstats = D.uase_batched(layers, max(DIMS), chunk, l=l, tol=1e-5, max_iters=400, check_dims=DIMS)
+                batch_log.append(bstats)
+            else:
+                solved = [(lambda r: (r[0], r[1], r[3]))(D.uase(layers, max(DIMS), l=l, tol=1e-5, max_iters=400, seed=seed, check_dims=DIMS))
+                          for seed in chunk]
+            for emb, _, info in solved:
+                infos.append(info)
+                local.append(D.distances(emb, cdims, cmets, strategy))
         sc = torch.stack(local) if local else torch.empty((0, T - 1, len(cdims), n), dtype=torch.float64, device=env.dev)
         if env.world > 1:
             sc = ND.gather_blocks(sc, len(seeds))
@@ -786,7 +802,8 @@ def run_b200_c5(args, w):
     ms_step, results, clocks = env.timed(step, args.steps, args.warmup)
     infos = [i for r in results for i in r[0]]
     launches = sum(r[2] for r in results)
-    roofline = stream_roofline(env, infos, ms_step, args.steps, n, layers[0].n_planes, l, args.workload)
+    roofline = stream_roofline(env, infos, ms_step, args.steps, n, layers[0].n_planes, l, args.workload, layers)
+    layer_storage = layers[0].storage
     e2e = None
     if not args.no_e2e:
         del layers
@@ -815,9 +832,14 @@ def run_b200_c5(args, w):
         "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": False, "scaling": "strong", "vs_baseline": None,
         "dtype": "bf16 planes x3-split bf16 operand, fp32 accumulate (tcgen05), fp64 small dense", "data": "synthetic",
         "config": {"workload": w["name"], "n": n, "layers": T, "communities": K, "block_width": l, "seeds": len(seeds),
-                   "seeds_per_gpu": len(mine), "planes_per_layer": 1, "l2_policy": "inputs larger than L2 (each layer pass streams 1.8 GB)",
+                   "seeds_per_gpu": len(mine), "planes_per_layer": 1, "layer_storage": layer_storage,
+                   "l2_policy": "inputs larger than L2 (each layer pass streams 0.9-1.8 GB)",
                    "operator_applications_per_run": [i["iterations"] for i in results[-1][0]],
-                   "all_converged": all(i["converged"] for i in infos), "setup_s": setup_s},
+                   "all_converged": all(i["converged"] for i in infos), "setup_s": setup_s,
+                   "seed_batch": group if batchable else 1,
+                   "layer_streams_per_step": (sum(b["layer_streams"] for b in batch_log[-max(len(batch_log) // max(args.steps + args.warmup, 1), 1):])
+                                              if batch_log else sum(i["layer_passes"] for i in results[-1][0])),
+                   "layer_passes_requested_per_step": sum(i["layer_passes"] for i in results[-1][0])},
         "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
     }
     print(json.dumps(line), flush=True)

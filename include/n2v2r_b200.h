@@ -48,8 +48,9 @@ typedef enum { N2V2R_F32 = 0, N2V2R_F64 = 1 } n2v2r_dtype_t;
 typedef enum { N2V2R_EUCLIDEAN = 0, N2V2R_COSINE = 1, N2V2R_CORRELATION = 2 } n2v2r_metric_t;
 typedef enum { N2V2R_SEQUENTIAL = 0, N2V2R_ONE_VS_BEFORE = 1, N2V2R_ONE_VS_REST = 2 } n2v2r_strategy_t;
 typedef enum { N2V2R_ALGO_TCGEN05 = 0, N2V2R_ALGO_SIMT = 1 } n2v2r_algo_t;
-/* how a layer is held in HBM: dense bf16 planes, or compressed tiles (sparse layers, expanded in shared memory) */
-typedef enum { N2V2R_STORE_PLANES = 0, N2V2R_STORE_TILES = 1 } n2v2r_storage_t;
+/* how a layer is held in HBM: dense bf16 planes; compressed tiles (sparse layers, expanded in shared memory); or ONE e4m3
+ * plane of 1 byte per entry (binarised layers and any layer whose entries e4m3 represents exactly) */
+typedef enum { N2V2R_STORE_PLANES = 0, N2V2R_STORE_TILES = 1, N2V2R_STORE_E4M3 = 2 } n2v2r_storage_t;
 
 int n2v2r_abi_version(void);
 const char* n2v2r_last_error(void);
@@ -104,6 +105,10 @@ int n2v2r_transform(void* stream, const void* d_in, int dtype, int64_t rows, int
  * exactly.  Synchronises `stream`. */
 int n2v2r_planes_needed(void* stream, const float* d_in, int64_t rows, int64_t cols, int64_t ld,
                         int* h_planes);
+/* One bf16 plane -> e4m3 bytes (rows x ld8, ld8 a multiple of 128, padding zero): the N2V2R_STORE_E4M3 form of a layer.
+ * *h_exact = 1 when every value is representable (then the layer is exact); synchronises `stream`. */
+int n2v2r_plane_to_e4m3(void* stream, const void* d_plane, int64_t rows, int64_t cols, int64_t ld_p,
+                        void* d_out, int64_t ld8, int* h_exact);
 /* 1 if the square plane set is symmetric (columns >= n of the padding are ignored).  ld_p must be a
  * multiple of 64 and d_planes 16-byte aligned.  Synchronises `stream`. */
 int n2v2r_is_symmetric(void* stream, const void* d_planes, int n_planes, int64_t n, int64_t ld_p,
@@ -163,7 +168,7 @@ int n2v2r_project(void* stream, const void* d_W, int dtype, int64_t rows, int64_
  * over all processes, in place, ordered on `stream`.
  * ---------------------------------------------------------------------------------- */
 typedef struct {
-  const void* d_planes;    /* N2V2R_STORE_PLANES: n_planes planes, each n x ld bf16         */
+  const void* d_planes;    /* PLANES: n_planes planes, each n x ld bf16; E4M3: one plane n x ld bytes (ld % 128 == 0) */
   const void* d_planes_t;  /* planes of A^T, or NULL when the layer is symmetric         */
   int32_t n_planes;        /* planes stored (PLANES) / plane terms the values need (TILES) */
   int32_t storage;         /* n2v2r_storage_t                                            */
@@ -201,6 +206,9 @@ typedef struct {
   int32_t trace;           /* 1 = one line per outer iteration on stderr                 */
   int32_t comm_mode;       /* how Y is summed over the processes: 0 = `allreduce` callback, 1 = `user` is an
                               ncclComm_t and the library calls ncclAllReduce itself on `stream` */
+  void* batch;             /* seed batching: handle of n2v2r_batch_create shared by concurrent solves, or NULL */
+  int32_t batch_slot;      /* this solve's slot in the batch, 0 .. participants-1                              */
+  int32_t reserved2;
 } n2v2r_uase_params_t;
 
 #define N2V2R_MAX_CHECK 32
@@ -241,6 +249,20 @@ int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2r_layer_t* 
                void* d_ws, size_t ws_bytes, n2v2r_allreduce_fn allreduce, void* user,
                float* d_embed /* T_local x n x k */, float* d_left /* n x k or NULL */,
                double* h_sigma /* k */, n2v2r_uase_stats_t* h_stats);
+
+/* ------------------------------------------------------------------------------------
+ * Seed batching (stability runs: README.md:54, :173; BASELINE configs[4]).  `participants` solves on the same resident,
+ * unsharded layers run concurrently -- one host thread and one stream each, each calling n2v2r_uase with params.batch =
+ * the handle and its own params.batch_slot, seed, workspace and outputs -- and every product M X they need is served for
+ * all waiting solves with ONE pass over each layer per up-to-three operands (bf16-plane layers; other storages are served
+ * one by one).  Every solve returns exactly the bits of the unbatched solve.  The handle owns a stream and events; d_ws is
+ * the batch's own operand / partial-sum workspace.  n2v2r_batch_destroy synchronises and reports
+ * {products served, layer passes, MMA milliseconds, MMA launches}.
+ * ---------------------------------------------------------------------------------- */
+size_t n2v2r_batch_workspace_bytes(const n2v2r_uase_params_t* p, int participants);
+int n2v2r_batch_create(const n2v2r_uase_params_t* p, const n2v2r_layer_t* h_layers, int participants,
+                       void* d_ws, size_t ws_bytes, void** handle);
+int n2v2r_batch_destroy(void* handle, double* h_stats4);
 
 /* One streaming skinny product, exposed for tests / roofline measurement:
  * d_out (n x l fp32) = A X  (transpose=0) or A^T X (transpose=1), X = d_x (n x l fp32). */

@@ -27,7 +27,7 @@ class NativeError(RuntimeError):
         self.status = status
 
 
-STORE_PLANES, STORE_TILES = 0, 1
+STORE_PLANES, STORE_TILES, STORE_E4M3 = 0, 1, 2
 MAX_CHECK = 32
 
 
@@ -44,7 +44,8 @@ class UaseParams(C.Structure):
                 ("cheb_degree", C.c_int32), ("algo", C.c_int32), ("k_chunk", C.c_int32), ("n_check", C.c_int32),
                 ("tol", C.c_double), ("seed", C.c_uint64), ("h_check_dims", C.POINTER(C.c_int32)),
                 ("floor_mult", C.c_double), ("rel_floor", C.c_double), ("first_degree", C.c_int32), ("no_early_lock", C.c_int32),
-                ("trace", C.c_int32), ("comm_mode", C.c_int32)]
+                ("trace", C.c_int32), ("comm_mode", C.c_int32), ("batch", C.c_void_p), ("batch_slot", C.c_int32),
+                ("reserved2", C.c_int32)]
 
 
 class UaseStats(C.Structure):
@@ -70,6 +71,7 @@ SIGNATURES = {
                                   C.POINTER(_i64), C.POINTER(_d), C.POINTER(_d), C.POINTER(_d)]),
     "n2v2r_transform": (_i, [_vp, _vp, _i, _i64, _i64, _i64, _i, _i, _d, _i, _d, _i, _vp, _i64, _vp, _i, _i64, _vp]),
     "n2v2r_planes_needed": (_i, [_vp, _vp, _i64, _i64, _i64, C.POINTER(_i)]),
+    "n2v2r_plane_to_e4m3": (_i, [_vp, _vp, _i64, _i64, _i64, _vp, _i64, C.POINTER(_i)]),
     "n2v2r_is_symmetric": (_i, [_vp, _vp, _i, _i64, _i64, C.POINTER(_i)]),
     "n2v2r_transpose_planes": (_i, [_vp, _vp, _i, _i64, _i64, _vp]),
     "n2v2r_tiles_count": (_i, [_vp, _vp, _i64, _i64, _vp, _vp, C.POINTER(_i), C.POINTER(_i)]),
@@ -81,6 +83,9 @@ SIGNATURES = {
     "n2v2r_uase_workspace_bytes": (_sz, [C.POINTER(UaseParams)]),
     "n2v2r_uase": (_i, [_vp, C.POINTER(UaseParams), C.POINTER(Layer), _vp, _sz, ALLREDUCE_FN, _vp, _vp, _vp,
                         C.POINTER(_d), C.POINTER(UaseStats)]),
+    "n2v2r_batch_workspace_bytes": (_sz, [C.POINTER(UaseParams), _i]),
+    "n2v2r_batch_create": (_i, [C.POINTER(UaseParams), C.POINTER(Layer), _i, _vp, _sz, C.POINTER(_vp)]),
+    "n2v2r_batch_destroy": (_i, [_vp, C.POINTER(_d)]),
     "n2v2r_comm_unique_id": (_i, [_vp]),
     "n2v2r_comm_init": (_i, [_vp, _i, _i, C.POINTER(_vp)]),
     "n2v2r_comm_destroy": (_i, [_vp]),

@@ -13,6 +13,8 @@ namespace n2v2r {
 
 int stream_apply_tcgen05(cudaStream_t s, const StreamPlan& plan, const void* planes, int n_planes, int64_t ld,
                          const float* x, __nv_bfloat16* xs, float* parts, float* out, int accumulate);  // k3_tcgen05.cu
+int stream_apply_e4m3(cudaStream_t s, const StreamPlan& plan, const void* plane8, int64_t ld8, const float* x, void* xs_ws,
+                      float* parts, float* out, int accumulate);                                        // k3_fp8.cu
 int stream_apply_tiles(cudaStream_t s, const StreamPlan& plan, const uint32_t* tile_ptr, const void* entries, int n_planes,
                        int tile_rows, const float* x, __nv_bfloat16* xs, float* parts, float* out, int accumulate);   // k3_sparse.cu
 
@@ -88,8 +90,9 @@ int make_stream_plan(int64_t n, int l, int algo, int k_chunk, StreamPlan* plan) 
   plan->k_chunk = k_chunk;
   plan->n_splits = (int)((plan->n_pad + k_chunk - 1) / k_chunk);
   if (algo == N2V2R_ALGO_TCGEN05) {
-    plan->xs_bytes = align_up(sizeof(__nv_bfloat16) * 3 * (size_t)l * plan->n_pad);
-    plan->part_bytes = align_up(sizeof(float) * (size_t)plan->n_splits * round_up(n, 256) * l);
+    // + room for the e4m3 operand (K padded to 128, column maxima and scales) and one more K split (k3_fp8.cu)
+    plan->xs_bytes = align_up(sizeof(__nv_bfloat16) * 3 * (size_t)l * plan->n_pad) + 65536;
+    plan->part_bytes = align_up(sizeof(float) * (size_t)(plan->n_splits + 1) * round_up(n, 256) * l);
   } else {
     plan->xs_bytes = 0;
     plan->part_bytes = 0;
@@ -107,6 +110,12 @@ int stream_apply(cudaStream_t s, const StreamPlan& plan, const n2v2r_layer_t& L,
       *bytes_moved += 8.0 * (double)((transpose && L.d_entries_t) ? L.n_entries_t : L.n_entries) +
                       4.0 * (double)((plan.n + L.tile_rows - 1) / L.tile_rows) * (double)(plan.n_pad / 64) + 4.0 * plan.l * 2.0 * (double)plan.n;
     return stream_apply_tiles(s, plan, tp, en, L.n_planes, L.tile_rows, x, xs, parts, out, accumulate);
+  }
+  if (L.storage == N2V2R_STORE_E4M3) {
+    const void* p8 = (transpose && L.d_planes_t) ? L.d_planes_t : L.d_planes;
+    N2V2R_REQUIRE(plan.algo == N2V2R_ALGO_TCGEN05, "e4m3 layers run on the tcgen05 path only");
+    if (bytes_moved) *bytes_moved += (double)plan.n * (double)plan.n + 4.0 * plan.l * 2.0 * (double)plan.n;
+    return stream_apply_e4m3(s, plan, p8, L.ld, x, xs, parts, out, accumulate);
   }
   const void* planes = (transpose && L.d_planes_t) ? L.d_planes_t : L.d_planes;
   N2V2R_REQUIRE(planes && L.n_planes >= 1 && L.n_planes <= 3 && L.ld >= plan.n && L.ld % 64 == 0,

@@ -19,6 +19,7 @@ struct StreamArgs {
   int n_planes, l, mh;              // planes, block width, 128-row halves per tile (1 or 2)
   int stages, n_tiles, n_splits, k_chunk;
   int n_jb;                         // column blocks of width l of the right operand (1 for the skinny products)
+  int nb;                           // operand blocks multiplied against ONE read of the A tile (seed batching; 1 otherwise)
   int upper_only;                   // SYRK: skip units entirely below the diagonal (projection)
   int64_t k_pad;                    // contraction length, multiple of 64
   int64_t rows_valid, cols_valid;   // extent of the output that may be written
@@ -39,8 +40,9 @@ __global__ void __launch_bounds__(192, 1) stream_mma_kernel(const __grid_constan
   const uint32_t bar_full = smem_u32(&bars[0]), bar_empty = smem_u32(&bars[8]);
   const uint32_t bar_tfull = smem_u32(&bars[16]), bar_tempty = smem_u32(&bars[17]);
   const int n_units = a.n_tiles * a.n_splits * a.n_jb;
-  const uint32_t tmem_cols = a.mh == 2 ? 512u : 256u;
   const int nacc = 3 * a.l;
+  uint32_t tmem_cols = 32u;
+  while (tmem_cols < (uint32_t)(a.nb * a.mh * nacc)) tmem_cols <<= 1;
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < a.stages; ++i) { mbar_init(bar_full + 8 * i, 1); mbar_init(bar_empty + 8 * i, 1); }
@@ -98,15 +100,18 @@ __global__ void __launch_bounds__(192, 1) stream_mma_kernel(const __grid_constan
         if (lane == 0) {
           const uint32_t base = smem0 + stage * a.stage_bytes;
           const uint32_t xbase = base + a.n_planes * a.a_plane_bytes;
-          for (int h = 0; h < a.mh; ++h) {
-            bool acc = !first;
-            for (int p = 0; p < a.n_planes; ++p) {
-              const uint32_t idesc = idesc_bf16((3 - p) * a.l);
-              const uint32_t abase = base + p * a.a_plane_bytes + h * 16384;
+          for (int bk = 0; bk < a.nb; ++bk) {
+            for (int h = 0; h < a.mh; ++h) {
+              bool acc = !first;
+              for (int p = 0; p < a.n_planes; ++p) {
+                const uint32_t idesc = idesc_bf16((3 - p) * a.l);
+                const uint32_t abase = base + p * a.a_plane_bytes + h * 16384;
 #pragma unroll
-              for (int k = 0; k < 4; ++k) {
-                umma_bf16(tmem_base + h * nacc, sw128_desc(abase + k * 32), sw128_desc(xbase + k * 32), idesc, acc ? 1u : 0u);
-                acc = true;
+                for (int k = 0; k < 4; ++k) {
+                  umma_bf16(tmem_base + (bk * a.mh + h) * nacc, sw128_desc(abase + k * 32), sw128_desc(xbase + bk * a.x_bytes + k * 32),
+                            idesc, acc ? 1u : 0u);
+                  acc = true;
+                }
               }
             }
           }
@@ -130,13 +135,14 @@ __global__ void __launch_bounds__(192, 1) stream_mma_kernel(const __grid_constan
       if (a.upper_only && (jb + 1) * a.l <= tile * 128 * a.mh) continue;
       mbar_wait(bar_tfull, uphase);
       tc_fence_after();
+      for (int bk = 0; bk < a.nb; ++bk)
       for (int h = 0; h < a.mh; ++h) {
         const int64_t row = (int64_t)tile * 128 * a.mh + h * 128 + q * 32 + lane;
-        float* dst = a.out + (size_t)split * a.split_stride + (size_t)row * a.out_ld + (size_t)jb * a.l;
-        const int64_t col_base = (int64_t)jb * a.l;
+        float* dst = a.out + (size_t)split * a.split_stride + (size_t)row * a.out_ld + (size_t)(jb + bk) * a.l;
+        const int64_t col_base = (int64_t)(jb + bk) * a.l;
         const bool row_ok = row < a.rows_valid;
         const bool vec_ok = row_ok && (a.out_ld % 4 == 0) && (col_base + a.l <= a.cols_valid);
-        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + h * nacc;
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (bk * a.mh + h) * nacc;
         for (int c0 = 0; c0 < a.l; c0 += 16) {
           uint32_t hi[16], mid[16], lo[16];
           tmem_ld16(taddr + c0, hi);
@@ -189,6 +195,24 @@ __global__ void __launch_bounds__(256) reduce_parts_kernel(const float* __restri
   reinterpret_cast<float4*>(out)[e4] = s;
 }
 
+
+// the same with the partials of one operand block inside a wider row: parts[s][row][col_off + c], row stride ld_parts
+__global__ void __launch_bounds__(256) reduce_parts_strided_kernel(const float* __restrict__ parts, int n_splits, int64_t split_stride,
+                                                                   int64_t ld_parts, int col_off, int64_t n, int l,
+                                                                   float* __restrict__ out, int accumulate) {
+  const int64_t e4 = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  const int64_t total4 = n * l / 4;
+  if (e4 >= total4) return;
+  const int l4 = l / 4;
+  const int64_t row = e4 / l4;
+  const int c4 = (int)(e4 - row * l4);
+  float4 s = accumulate ? reinterpret_cast<const float4*>(out)[e4] : make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int sp = 0; sp < n_splits; ++sp) {
+    const float4 v = *reinterpret_cast<const float4*>(parts + (size_t)sp * split_stride + row * ld_parts + col_off + 4 * c4);
+    s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+  }
+  reinterpret_cast<float4*>(out)[e4] = s;
+}
 
 // ---- projection epilogue: out[i][j] = out[j][i] = sum_s parts[s][i][j] for i <= j (fixed order; exactly symmetric) ----
 __global__ void __launch_bounds__(256) mirror_reduce_kernel(const float* __restrict__ parts, int n_splits, int64_t split_stride,
@@ -287,29 +311,40 @@ static PFN_cuTensorMapEncodeTiled_v12000 get_encode() {
 }
 
 // bf16 tensor map, SWIZZLE_128B, rank 2 or 3 (inner box = 64 elements = 128 B)
-int make_map(CUtensorMap* map, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
-                    const uint32_t* box) {
+static int make_map_typed(CUtensorMap* map, CUtensorMapDataType dt, const void* base, int rank, const uint64_t* dims,
+                          const uint64_t* strides_bytes, const uint32_t* box) {
   PFN_cuTensorMapEncodeTiled_v12000 enc = get_encode();
   if (!enc) { set_error("cuTensorMapEncodeTiled entry point not available"); return N2V2R_ECUDA; }
   cuuint64_t d[3]; cuuint64_t st[2]; cuuint32_t bx[3]; cuuint32_t es[3] = {1, 1, 1};
   for (int i = 0; i < rank; ++i) { d[i] = dims[i]; bx[i] = box[i]; }
   for (int i = 0; i < rank - 1; ++i) st[i] = strides_bytes[i];
-  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), d, st, bx, es,
+  CUresult r = enc(map, dt, (cuuint32_t)rank, const_cast<void*>(base), d, st, bx, es,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed with %d", (int)r); return N2V2R_ECUDA; }
   return N2V2R_OK;
 }
+int make_map(CUtensorMap* map, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+             const uint32_t* box) {
+  return make_map_typed(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, base, rank, dims, strides_bytes, box);
+}
+int make_map_u8(CUtensorMap* map, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                const uint32_t* box) {
+  return make_map_typed(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, base, rank, dims, strides_bytes, box);
+}
 
 // D[m_rows x (n_jb*l)] = A[m_rows x k] * B^T, A = n_planes planes (row stride lda), B = 3 split planes [3][b_rows][ldb]
 static int launch_mma(cudaStream_t s, const void* a_planes, int n_planes, int64_t m_rows, int64_t lda, size_t a_plane_stride,
                       const void* b_planes, int64_t b_rows, int64_t ldb, int l, int n_jb, int64_t k_pad, int k_chunk,
-                      float* out, int64_t out_ld, int64_t split_stride, int64_t rows_valid, int64_t cols_valid, int upper_only = 0) {
+                      float* out, int64_t out_ld, int64_t split_stride, int64_t rows_valid, int64_t cols_valid, int upper_only = 0,
+                      int nb = 1) {
   StreamArgs a;
   a.upper_only = upper_only;
   a.n_planes = n_planes;
   a.l = l;
-  a.mh = n_planes == 1 ? 2 : 1;
+  a.nb = nb;
+  a.mh = (n_planes == 1 && nb == 1) ? 2 : 1;
+  N2V2R_REQUIRE(nb >= 1 && nb * a.mh * 3 * l <= 512, "tcgen05 path: %d operand blocks of width %d do not fit in TMEM", nb, l);
   a.k_chunk = k_chunk;
   a.k_pad = k_pad;
   a.n_splits = (int)((k_pad + k_chunk - 1) / k_chunk);
@@ -317,7 +352,7 @@ static int launch_mma(cudaStream_t s, const void* a_planes, int n_planes, int64_
   a.n_tiles = (int)((m_rows + 128 * a.mh - 1) / (128 * a.mh));
   a.a_plane_bytes = 16384u * a.mh;
   a.x_bytes = 3u * l * 128u;                       // multiple of 1024 because l % 16 == 0
-  a.stage_bytes = n_planes * a.a_plane_bytes + a.x_bytes;
+  a.stage_bytes = n_planes * a.a_plane_bytes + nb * a.x_bytes;
   a.out = out;
   a.out_ld = out_ld;
   a.split_stride = split_stride;
@@ -337,9 +372,9 @@ static int launch_mma(cudaStream_t s, const void* a_planes, int n_planes, int64_
     if (rc) return rc;
   }
   {
-    const uint64_t dims[3] = {(uint64_t)ldb, (uint64_t)b_rows, 3};
+    const uint64_t dims[3] = {(uint64_t)ldb, (uint64_t)b_rows, (uint64_t)(3 * nb)};     // batched: [nb][3][l][ldb], b_rows == l
     const uint64_t str[2] = {(uint64_t)ldb * 2, (uint64_t)b_rows * ldb * 2};
-    const uint32_t box[3] = {64, (uint32_t)l, 3};
+    const uint32_t box[3] = {64, (uint32_t)l, (uint32_t)(3 * nb)};
     int rc = make_map(&mX, b_planes, 3, dims, str, box);
     if (rc) return rc;
   }
@@ -369,6 +404,31 @@ int stream_apply_tcgen05(cudaStream_t s, const StreamPlan& plan, const void* pla
                   plan.n_pad, plan.k_chunk, parts, plan.l, rows_pad * plan.l, rows_pad, plan.l);
   if (rc) return rc;
   return launch_reduce_parts(s, parts, plan.n_splits, rows_pad, plan.n, plan.l, out, accumulate);
+}
+
+// Seed batching: out_i (= or +=) A x_i for nb operands with ONE read of the layer.  xs: [nb][3][l][n_pad] bf16, parts:
+// [n_splits][rows_pad][nb * l].  Every out_i has exactly the bits of the unbatched product (same K split, same MMA order per
+// row; the 128- instead of 256-row tiles do not change a row's accumulation).
+int stream_apply_batched(cudaStream_t s, const StreamPlan& plan, const void* planes, int n_planes, int64_t ld, int nb,
+                         const float* const* x, __nv_bfloat16* xs, float* parts, float* const* out, int accumulate) {
+  N2V2R_REQUIRE(xs && parts && nb >= 1 && nb <= 3, "batched product: bad arguments");
+  const size_t per = (size_t)3 * plan.l * plan.n_pad;
+  for (int i = 0; i < nb; ++i) {
+    int rc = launch_split_transpose(s, x[i], plan.n, plan.l, plan.n_pad, xs + i * per);
+    if (rc) return rc;
+  }
+  const int64_t rows_pad = round_up(plan.n, 256);
+  const int64_t ldp = (int64_t)nb * plan.l;
+  int rc = launch_mma(s, planes, n_planes, plan.n, ld, (size_t)plan.n * ld * sizeof(__nv_bfloat16), xs, plan.l, plan.n_pad, plan.l, 1,
+                      plan.n_pad, plan.k_chunk, parts, ldp, rows_pad * ldp, rows_pad, ldp, 0, nb);
+  if (rc) return rc;
+  for (int i = 0; i < nb; ++i) {
+    const int64_t total4 = plan.n * plan.l / 4;
+    reduce_parts_strided_kernel<<<(unsigned)((total4 + 255) / 256), 256, 0, s>>>(parts, plan.n_splits, rows_pad * ldp, ldp, i * plan.l,
+                                                                                plan.n, plan.l, out[i], accumulate);
+    N2V2R_CHECK_LAUNCH();
+  }
+  return N2V2R_OK;
 }
 
 int launch_reduce_parts(cudaStream_t s, const float* parts, int n_splits, int64_t rows_pad, int64_t n, int l, float* out, int accumulate) {

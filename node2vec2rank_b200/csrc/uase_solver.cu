@@ -29,6 +29,8 @@
 namespace n2v2r {
 
 int comm_allreduce_f32(void* comm, float* d_buf, int64_t count, cudaStream_t s);   // comm.cu
+int batch_apply(void* handle, int slot, const float* x, float* out, float* z_keep, float* zt, cudaStream_t s);   // batch.cu
+void batch_leave(void* handle, int slot);
 
 struct SolverBufs {
   float *Q, *Y, *Qn, *Qw, *X0, *X1, *X2, *Zt;
@@ -92,8 +94,13 @@ static double cheb_T(double x, int m) { return cosh((double)m * acosh(x > 1.0 ? 
 extern "C" int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2r_layer_t* L, void* d_ws, size_t ws_bytes,
                           n2v2r_allreduce_fn allreduce, void* user, float* d_embed, float* d_left, double* h_sigma,
                           n2v2r_uase_stats_t* st) {
+  struct LeaveBatch {                      // however the solve ends, the other solves of the batch stop waiting for it
+    void* b; int slot;
+    ~LeaveBatch() { if (b) batch_leave(b, slot); }
+  } leave_batch{p ? p->batch : nullptr, p ? p->batch_slot : 0};
   RC(check_params(p));
   N2V2R_REQUIRE(L && d_ws && d_embed && h_sigma, "uase: null pointer");
+  N2V2R_REQUIRE(!p->batch || p->T_local == p->T_global, "uase: seed batching runs on unsharded layers");
   N2V2R_REQUIRE(allreduce || p->T_local == p->T_global || (p->comm_mode == 1 && user),
                 "uase: sharded layers need an all-reduce callback or an NCCL communicator (comm_mode = 1)");
   cudaStream_t s = (cudaStream_t)stream;
@@ -140,10 +147,14 @@ extern "C" int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2
     N2V2R_CUDA(cudaEventCreate(&e0));
     N2V2R_CUDA(cudaEventCreate(&e1));
     N2V2R_CUDA(cudaEventRecord(e0, s));
-    for (int t = 0; t < T; ++t) {
-      float* z = keep_z ? b.Z + t * nl : b.Zt;
-      RC(stream_apply(s, plan, L[t], 1, x, b.xs, b.parts, z, 0, &stats.stream_bytes));       // Z_t = A_t^T x
-      RC(stream_apply(s, plan, L[t], 0, z, b.xs, b.parts, out, t > 0, &stats.stream_bytes));  // out += A_t Z_t
+    if (p->batch) {                          // served together with the other solves of the batch (batch.cu)
+      RC(batch_apply(p->batch, p->batch_slot, x, out, keep_z ? b.Z : nullptr, b.Zt, s));
+    } else {
+      for (int t = 0; t < T; ++t) {
+        float* z = keep_z ? b.Z + t * nl : b.Zt;
+        RC(stream_apply(s, plan, L[t], 1, x, b.xs, b.parts, z, 0, &stats.stream_bytes));       // Z_t = A_t^T x
+        RC(stream_apply(s, plan, L[t], 0, z, b.xs, b.parts, out, t > 0, &stats.stream_bytes));  // out += A_t Z_t
+      }
     }
     N2V2R_CUDA(cudaEventRecord(e1, s));
     evs.push_back(e0); evs.push_back(e1);

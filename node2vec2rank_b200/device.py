@@ -57,7 +57,7 @@ class DeviceLayer:
                            0 if self.entries_t is None else self.entries_t.data_ptr(),
                            self.n_entries, self.n_entries_t, self.tile_rows, 0)
         return N.Layer(self.planes.data_ptr(), 0 if self.planes_t is None else self.planes_t.data_ptr(),
-                       self.n_planes, N.STORE_PLANES, self.ld, 0, 0, 0, 0, 0, 0, 0, 0)
+                       self.n_planes, N.STORE_E4M3 if self.storage == "e4m3" else N.STORE_PLANES, self.ld, 0, 0, 0, 0, 0, 0, 0, 0)
 
     def to_dense(self):
         """fp32 (n, n) device tensor reconstructed from the stored form (exact)."""
@@ -66,7 +66,30 @@ class DeviceLayer:
             N.check(N.load().n2v2r_tiles_to_dense(N.stream_ptr(), N.ptr(self.tile_ptr), N.ptr(self.entries), self.n, self.tile_rows,
                                                   N.ptr(out), self.n))
             return out
+        if self.storage == "e4m3":
+            return self.planes[0, :, :self.n].view(torch.float8_e4m3fn).to(torch.float32)
         return self.planes[:, :, :self.n].to(torch.float32).sum(dim=0)
+
+    def to_e4m3(self):
+        """The same layer as ONE e4m3 plane (1 byte per entry, N2V2R_STORE_E4M3): for one-plane layers whose values e4m3
+        represents exactly (binarised layers).  Raises ValueError otherwise."""
+        if self.storage == "e4m3":
+            return self
+        if self.storage != "planes" or self.n_planes != 1:
+            raise ValueError("only one-plane bf16 layers can be stored as e4m3")
+        lib = N.load()
+        ld8 = (self.n + 127) // 128 * 128
+
+        def conv(p):
+            out = torch.empty((1, self.n, ld8), dtype=torch.uint8, device=p.device)
+            exact = C.c_int(0)
+            N.check(lib.n2v2r_plane_to_e4m3(N.stream_ptr(), N.ptr(p), self.n, self.n, self.ld, N.ptr(out), ld8, C.byref(exact)))
+            if not exact.value:
+                raise ValueError("layer values are not exactly representable in e4m3")
+            return out
+
+        return DeviceLayer(planes=conv(self.planes), n=self.n, ld=ld8, n_planes=1, symmetric=self.symmetric,
+                           planes_t=None if self.planes_t is None else conv(self.planes_t), colsum=self.colsum, storage="e4m3")
 
     def numpy(self):
         return self.to_dense().cpu().numpy()
@@ -79,7 +102,7 @@ class DeviceLayer:
     def nbytes(self):
         if self.storage == "tiles":
             return (self.n_entries + self.n_entries_t) * 8 + sum(t.numel() * 4 for t in (self.tile_ptr, self.tile_ptr_t) if t is not None)
-        return self.planes.numel() * 2 * (2 if self.planes_t is not None else 1)
+        return self.planes.numel() * self.planes.element_size() * (2 if self.planes_t is not None else 1)
 
 
 def _dtype_code(t: torch.Tensor):
@@ -293,6 +316,7 @@ def project(W: torch.Tensor, on):
     return out
 
 
+E4M3_AUTO = False               # storage="auto": binarised layers as one e4m3 plane (set after measuring, see profiles/)
 TILES_MAX_DENSITY = 0.08        # layers sparser than this are stored as compressed tiles (storage="auto")
 TILES_MIN_N = 4096              # ... when they are large enough for the streaming product to matter
 
@@ -342,8 +366,10 @@ def make_layer(x32: torch.Tensor, n_planes=None, colsum=None, check_symmetry=Tru
     TILES_MAX_DENSITY and n >= TILES_MIN_N; "tiles": always), else bf16 planes + symmetry flag / transposed copy."""
     n = x32.shape[0]
     assert x32.shape[0] == x32.shape[1], "layer must be square"
-    if storage not in ("auto", "planes", "tiles"):
+    if storage not in ("auto", "planes", "tiles", "e4m3"):
         raise ValueError(f"unknown layer storage {storage!r}")
+    if storage == "e4m3":
+        return make_layer(x32, n_planes=1, colsum=colsum, check_symmetry=check_symmetry, storage="planes").to_e4m3()
     known_sym = None
     if storage == "tiles" or (storage == "auto" and n >= TILES_MIN_N and n_planes is None):
         layer, P, known_sym = make_tiles_layer(x32, colsum=colsum, max_density=None if storage == "tiles" else TILES_MAX_DENSITY)
@@ -585,6 +611,8 @@ def preprocess_to_layer(x: torch.Tensor, threshold=None, top_percent_keep=100, b
         cut = percentile_cut(x, 100 - top_percent_keep, absolute, threshold)
     n = x.shape[0]
     check_sym = not projected            # K2 mirrors the upper triangle: W^T W is exactly symmetric, and K1b is elementwise
+    if storage == "e4m3" and not binarize:
+        raise ValueError('layer storage "e4m3" needs binarised layers (values exactly representable in e4m3)')
     if binarize and storage != "tiles":
         P = 1
     elif storage_planes and storage != "tiles":
@@ -601,7 +629,10 @@ def preprocess_to_layer(x: torch.Tensor, threshold=None, top_percent_keep=100, b
         return layer, (out if want_f32 else None)
     out, planes, ld_p, cs = transform(x, absolute, threshold, cut, binarize, want_f32=want_f32, n_planes=P,
                                       want_colsum=True)
-    return finish_layer(planes, n, ld_p, P, cs, check_sym), out
+    layer = finish_layer(planes, n, ld_p, P, cs, check_sym)
+    if storage == "e4m3" or (storage == "auto" and binarize and E4M3_AUTO and n >= TILES_MIN_N):
+        layer = layer.to_e4m3()          # {0, 1} is exact in e4m3: half the bytes of the bf16 plane
+    return layer, out
 
 
 CONVERGED_STATUS = {0: "max_iters", 1: "converged", 2: "stagnated"}
@@ -668,6 +699,86 @@ def uase(layers, k, l=64, tol=1e-5, max_iters=300, min_iters=2, seed=42, check_d
                 angle_bounds={int(d): float(stats.angle_bounds[i]) for i, d in enumerate(dims)},
                 resid=np.asarray(stats.resid[:l]), ritz=np.asarray(stats.ritz[:l]), status=rc, l=l)
     return emb, sigma, left, info
+
+
+def uase_batched(layers, k, seeds, l=64, tol=1e-5, max_iters=300, min_iters=2, check_dims=None, k_chunk=0, cheb_degree=0):
+    """Seed batching (stability runs): one UASE solve per seed on the same resident layers, run CONCURRENTLY -- a host thread
+    and a CUDA stream per solve -- with every product M X served for all waiting solves by one pass over each layer per up
+    to three operands (n2v2r_batch_*, csrc/batch.cu).  Each solve is bit-identical to device.uase(layers, k, seed=...).
+    Returns ([(emb, sigma, info)] in the order of `seeds`, batch stats dict)."""
+    import threading
+    lib = N.load()
+    dev = _dev()
+    seeds = [int(s) for s in seeds]
+    S = len(seeds)
+    if S == 0:
+        return [], {}
+    T, n = len(layers), layers[0].n
+    dims = np.asarray(sorted(set(int(d) for d in (check_dims or [k]) if 1 <= int(d) <= k)), dtype=np.int32)[-N.MAX_CHECK:]
+    arr = (N.Layer * T)(*[L.c_struct() for L in layers])
+
+    def params(seed=0, batch=None, slot=0):
+        return N.UaseParams(n=n, T_local=T, T_global=T, layer_offset=0, k=k, l=l, max_iters=max_iters, min_iters=min_iters,
+                            cheb_degree=cheb_degree, algo=N.ALGO_TCGEN05, k_chunk=k_chunk, n_check=len(dims), tol=tol, seed=seed,
+                            h_check_dims=dims.ctypes.data_as(C.POINTER(C.c_int32)), batch=batch, batch_slot=slot)
+
+    p0 = params()
+    ws_bytes = lib.n2v2r_uase_workspace_bytes(C.byref(p0))
+    if ws_bytes == 0:
+        raise N.NativeError(N.EINVAL, lib.n2v2r_last_error().decode())
+    bws = torch.empty(lib.n2v2r_batch_workspace_bytes(C.byref(p0), S), dtype=torch.uint8, device=dev)
+    handle = C.c_void_p()
+    N.check(lib.n2v2r_batch_create(C.byref(p0), arr, S, N.ptr(bws), bws.numel(), C.byref(handle)))
+    main = torch.cuda.current_stream(dev)
+    # every buffer is allocated on the current stream before the solves start; the solve streams wait for it and are waited for
+    wss = [torch.empty(ws_bytes, dtype=torch.uint8, device=dev) for _ in range(S)]
+    embs = [torch.empty((T, n, k), dtype=torch.float32, device=dev) for _ in range(S)]
+    sigmas = [np.zeros(k, dtype=np.float64) for _ in range(S)]
+    stats = [N.UaseStats() for _ in range(S)]
+    streams = [torch.cuda.Stream(dev) for _ in range(S)]
+    rcs, errs = [None] * S, [None] * S
+    for st in streams:
+        st.wait_stream(main)
+
+    def run(i):
+        try:
+            torch.cuda.set_device(dev)
+            p = params(seeds[i], handle, i)
+            rcs[i] = lib.n2v2r_uase(C.c_void_p(streams[i].cuda_stream), C.byref(p), arr, N.ptr(wss[i]), ws_bytes,
+                                    C.cast(None, N.ALLREDUCE_FN), None, N.ptr(embs[i]), None,
+                                    sigmas[i].ctypes.data_as(C.POINTER(C.c_double)), C.byref(stats[i]))
+            if rcs[i] not in (N.OK, N.ENOTCONV):
+                errs[i] = N.NativeError(rcs[i], lib.n2v2r_last_error().decode("utf-8", "replace"))
+        except BaseException as ex:  # noqa: BLE001
+            errs[i] = ex
+
+    threads = [threading.Thread(target=run, args=(i,), name=f"n2v2r-seed-{seeds[i]}") for i in range(S)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    for st in streams:
+        main.wait_stream(st)
+    b4 = (C.c_double * 4)()
+    brc = lib.n2v2r_batch_destroy(handle, b4)
+    for e in errs:
+        if e is not None:
+            raise e
+    N.check(brc)
+    out = []
+    for i in range(S):
+        st_ = stats[i]
+        info = dict(seed=seeds[i], iterations=st_.iterations, layer_passes=st_.layer_passes, converged=int(st_.converged),
+                    converged_status=CONVERGED_STATUS.get(int(st_.converged), "?"), bound_met=bool(st_.bound_met),
+                    kernel_launches=st_.kernel_launches, outer_iterations=st_.outer_iterations, locked=st_.locked,
+                    stream_ms=st_.stream_ms, mma_ms=b4[2] / S, mma_launches=b4[3] / S, total_ms=st_.total_ms, stream_bytes=st_.stream_bytes,
+                    angle_bound=st_.max_angle_bound, angle_bounds={int(d): float(st_.angle_bounds[j]) for j, d in enumerate(dims)},
+                    resid=np.asarray(st_.resid[:l]), ritz=np.asarray(st_.ritz[:l]), status=rcs[i], l=l,
+                    allreduce_calls=0, allreduce_bytes=0, allreduce_path="none")
+        out.append((embs[i], sigmas[i], info))
+    batch = dict(products=int(b4[0]), layer_streams=int(b4[1]), mma_ms=float(b4[2]), mma_launches=int(b4[3]),
+                 unbatched_layer_streams=int(sum(s_.layer_passes for s_ in stats)))
+    return out, batch
 
 
 def subspace_sin_angles(emb_a: torch.Tensor, emb_b: torch.Tensor, dims):
@@ -779,6 +890,6 @@ def default_block_width(k, n):
 
 def column_sums(layer: DeviceLayer):
     """Column sums (float64, device) of a DeviceLayer: sum over planes of the bf16 values (model.py:293-294)."""
-    if layer.storage == "tiles":
+    if layer.storage != "planes":
         return layer.to_dense().sum(dim=0, dtype=torch.float64)
     return layer.planes[:, :, :layer.n].to(torch.float64).sum(dim=(0, 1))

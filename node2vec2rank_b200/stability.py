@@ -51,6 +51,7 @@ class StabilityRun:
         self.pairwise_aggregate_ranks = None
         self.per_seed_aggregate_ranks = None
         self.solver_infos = []
+        self.batch_stats = []
         self._scores = None                 # (S, C, cols, n) float64, device
 
     def _my_seeds(self):
@@ -78,14 +79,29 @@ class StabilityRun:
         mine, sharded = self._my_seeds()
         local = []
         self.solver_infos = []
-        for seed in mine:
-            emb, _, _, info = D.uase(layers, k, l=l, tol=float(cfg.get("solver_tol", 1e-5)),
-                                     max_iters=int(cfg.get("solver_max_iters", 400)), seed=seed,
-                                     check_dims=m.embed_dimensions)
-            info["seed"] = seed
-            check_solver_outcome(info, cfg)
-            self.solver_infos.append(info)
-            local.append(D.distances(emb, dims, mets, strategy))          # (C, cols, n)
+        self.batch_stats = []
+        # "seed_batch" (additive config key, default 16): that many solves run concurrently and share every pass over a layer,
+        # three operands per pass (device.uase_batched); each solve is bit-identical to its unbatched run.  1 = one after the other.
+        group = max(1, min(16, int(cfg.get("seed_batch", 16))))
+        batchable = group > 1 and all(L.storage == "planes" for L in layers)
+        for g0 in range(0, len(mine), group if batchable else 1):
+            chunk = mine[g0:g0 + (group if batchable else 1)]
+            if batchable and len(chunk) > 1:
+                solved, bstats = D.uase_batched(layers, k, chunk, l=l, tol=float(cfg.get("solver_tol", 1e-5)),
+                                                max_iters=int(cfg.get("solver_max_iters", 400)), check_dims=m.embed_dimensions)
+                self.batch_stats.append(bstats)
+            else:
+                solved = []
+                for seed in chunk:
+                    emb, sigma, _, info = D.uase(layers, k, l=l, tol=float(cfg.get("solver_tol", 1e-5)),
+                                                 max_iters=int(cfg.get("solver_max_iters", 400)), seed=seed,
+                                                 check_dims=m.embed_dimensions)
+                    solved.append((emb, sigma, info))
+            for seed, (emb, _, info) in zip(chunk, solved):
+                info["seed"] = seed
+                check_solver_outcome(info, cfg)
+                self.solver_infos.append(info)
+                local.append(D.distances(emb, dims, mets, strategy))          # (C, cols, n)
         n_comp = len(layers) if strategy == N.ONE_VS_REST else len(layers) - 1
         shape = (max(n_comp, 0), len(dims), n)
         if local:

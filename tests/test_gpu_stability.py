@@ -82,3 +82,52 @@ def test_stability_errors(gpu):
         run.run(method="kemeny")
     with pytest.raises(ValueError):
         run.agreement()
+
+
+@pytest.mark.parametrize("n_seeds", [2, 4, 7])
+def test_seed_batched_solves_are_bit_identical_to_unbatched(gpu, n_seeds):
+    """device.uase_batched: concurrent solves that share every pass over a layer (three operands per pass, csrc/batch.cu)
+    return, seed by seed, exactly the bits of device.uase run alone -- including a non-symmetric and a two-plane layer."""
+    import torch
+    from node2vec2rank_b200 import device as D
+    from node2vec2rank_b200.synthetic import block_matrices, sbm_layer_numpy
+    n, K, T, k = 1800, 6, 3, 12
+    Bs, _ = block_matrices(K, T, seed=2)
+    graphs = [sbm_layer_numpy(n, K, Bs[t], 5, t, weighted=(t == 1)) for t in range(T)]
+    graphs[2] = np.triu(graphs[2]) + 0.5 * np.tril(graphs[2])                 # not symmetric
+    layers = [D.make_layer(torch.from_numpy(np.ascontiguousarray(g, dtype=np.float32)).to(gpu)) for g in graphs]
+    assert [L.n_planes for L in layers] == [1, 2, 1] and not layers[2].symmetric
+    seeds = list(range(11, 11 + n_seeds))
+    solo = [D.uase(layers, k, l=48, tol=1e-6, max_iters=300, seed=s, check_dims=[2, 4, K, k]) for s in seeds]
+    batched, stats = D.uase_batched(layers, k, seeds, l=48, tol=1e-6, max_iters=300, check_dims=[2, 4, K, k])
+    assert len(batched) == n_seeds
+    for (e1, s1, _, i1), (e2, s2, i2) in zip(solo, batched):
+        assert torch.equal(e1.view(torch.int32), e2.view(torch.int32))
+        assert np.array_equal(s1, s2) and i1["iterations"] == i2["iterations"] and i1["converged"] == i2["converged"]
+    # fewer passes over the layers than the solves asked for: up to three operands per pass
+    assert stats["unbatched_layer_streams"] == sum(i["layer_passes"] for _, _, _, i in solo)
+    assert stats["layer_streams"] < stats["unbatched_layer_streams"]
+    assert stats["layer_streams"] >= stats["unbatched_layer_streams"] / 3
+
+
+def test_stability_run_with_and_without_seed_batching(gpu):
+    import contextlib
+    import io
+    import torch
+    from node2vec2rank_b200.stability import StabilityRun
+    from node2vec2rank_b200.synthetic import block_matrices, sbm_layer_numpy
+    n, K, T = 1200, 5, 3
+    Bs, _ = block_matrices(K, T, seed=3)
+    graphs = [sbm_layer_numpy(n, K, Bs[t], 9, t) for t in range(T)]
+    out = {}
+    for batch in (1, 16):
+        cfg = dict(embed_dimensions=[2, 4, 6], distance_metrics=["euclidean", "cosine"], comp_strategy="sequential", seed=None,
+                   save_dir=None, verbose=-1, seed_batch=batch)
+        with contextlib.redirect_stdout(io.StringIO()):
+            run = StabilityRun(graphs=graphs, nodes=np.arange(n), config=cfg, seeds=[1, 2, 3, 4, 5])
+            agg = run.run()
+        out[batch] = (agg, run.pairwise_ranks, run.batch_stats)
+    assert out[16][2] and not out[1][2]
+    for key in out[1][0]:
+        assert np.array_equal(out[1][0][key].to_numpy(), out[16][0][key].to_numpy())
+        assert np.array_equal(out[1][1][key].to_numpy(), out[16][1][key].to_numpy())
