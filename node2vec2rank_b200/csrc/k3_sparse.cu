@@ -284,6 +284,7 @@ struct SparseArgs {
   uint32_t a_plane_bytes, a_stage_bytes, x_bytes;
   uint32_t off_x, off_land, off_undo;  // byte offsets from the 1024-aligned base (A stages start at 0)
   uint32_t tmem_cols;
+  int debug_mode;                      // profiling only (n2v2r__debug_sparse_mode): 1 = no scatter / restore, 2 = no MMA issue
   const uint32_t* tile_ptr;
   const uint2* entries;
   float* out;
@@ -356,7 +357,7 @@ __global__ void __launch_bounds__(384, 1) sparse_mma_kernel(const __grid_constan
         if (lane == 0) {
           const uint32_t abase0 = smem0 + as * a.a_stage_bytes;
           const uint32_t xbase = smem0 + a.off_x + xs * a.x_bytes;
-          for (int h = 0; h < a.mh; ++h) {
+          for (int h = 0; h < (a.debug_mode == 2 ? 0 : a.mh); ++h) {
             bool acc = !first;
             for (int p = 0; p < a.n_planes; ++p) {
               const uint32_t idesc = idesc_bf16((3 - p) * a.l);
@@ -472,7 +473,8 @@ __global__ void __launch_bounds__(384, 1) sparse_mma_kernel(const __grid_constan
         const uint32_t undo = smem0 + a.off_undo + as * (kUndoCap * 2);
         const uint32_t prev = as == 0 ? prev0 : as == 1 ? prev1 : as == 2 ? prev2 : prev3;
         mbar_wait(bar_aempty + 8 * as, pa ^ 1u);        // the MMAs that read this stage have retired
-        if (prev > (uint32_t)kUndoCap) {
+        if (a.debug_mode == 1) {
+        } else if (prev > (uint32_t)kUndoCap) {
           for (uint32_t i = ct; i < (a.a_stage_bytes >> 4); i += 128) st_shared_zero16(abase + (i << 4));
         } else {
           for (uint32_t i = ct; i < prev; i += 128) {
@@ -491,7 +493,7 @@ __global__ void __launch_bounds__(384, 1) sparse_mma_kernel(const __grid_constan
           const uint32_t c = lcnt[ls];
           const uint32_t nent = c & 0x7fffffffu;
           const uint32_t land = smem0 + a.off_land + ls * (kLandCap * 8);
-          for (uint32_t j = ct; j < nent; j += 128) {
+          for (uint32_t j = ct; j < (a.debug_mode == 1 ? 0u : nent); j += 128) {
             const uint2 ent = ld_shared_v2(land + 8 * j);
             const uint32_t pos = ent.x & 0xFFFFu;
             if (total + j < (uint32_t)kUndoCap) st_shared_u16(undo + 2 * (total + j), pos);
@@ -522,6 +524,7 @@ __global__ void __launch_bounds__(384, 1) sparse_mma_kernel(const __grid_constan
 }
 
 // ---- host ---------------------------------------------------------------------------------------
+static int g_sparse_debug_mode = 0;
 // K split that balances (row tiles x splits) units over the persistent CTAs
 static int pick_splits(int n_tiles, int n_kb, int max_splits, int grid) {
   int best = 1;
@@ -589,6 +592,7 @@ int stream_apply_tiles(cudaStream_t s, const StreamPlan& plan, const uint32_t* t
   a.cols_valid = plan.l;
   a.out_ld = plan.l;
   a.split_stride = rows_pad * plan.l;
+  a.debug_mode = g_sparse_debug_mode;
   a.tile_ptr = tile_ptr;
   a.entries = (const uint2*)entries;
   a.out = parts;
@@ -620,6 +624,9 @@ int stream_apply_tiles(cudaStream_t s, const StreamPlan& plan, const uint32_t* t
 }  // namespace n2v2r
 
 using namespace n2v2r;
+
+// profiling hook (not part of the ABI header): skip parts of the sparse product kernel to time the rest
+extern "C" void n2v2r__debug_sparse_mode(int mode) { g_sparse_debug_mode = mode; }
 
 // ---- C ABI: building the compressed tiles --------------------------------------------------------
 extern "C" int n2v2r_tiles_count(void* stream, const float* d_in, int64_t n, int64_t ld, uint32_t* d_counts, uint32_t* d_counts_t,

@@ -3,6 +3,7 @@
 set -u
 O=gpurun_out/r2c3; mkdir -p $O
 export N2V2R_TEST_LOG=$O/testlog
+timeout 300 python scripts/probe_tiles.py 50000 48 10 20 --only-tiles --debug-modes > $O/probe_tiles_modes.log 2>&1; tail -1 $O/probe_tiles_modes.log
 timeout 900 python -m pytest tests/test_gpu_fp8.py -q > $O/pytest_fp8.log 2>&1; echo "fp8 rc=$?" | tee $O/rc.txt
 timeout 900 python -m pytest tests/test_gpu_stability.py -q > $O/pytest_stability.log 2>&1; echo "stability rc=$?" | tee -a $O/rc.txt
 timeout 1800 python -m pytest tests -m gpu -q --deselect tests/test_gpu_fp8.py --deselect tests/test_gpu_stability.py > $O/pytest_gpu.log 2>&1; echo "gpu rc=$?" | tee -a $O/rc.txt

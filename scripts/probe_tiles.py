@@ -40,6 +40,12 @@ def timed(layer, k_chunk=0):
 
 ms_t, y_t = timed(Lt)
 out["tiles_ms"] = ms_t
+if "--debug-modes" in sys.argv:                 # profiling: the kernel without its converters / without its MMAs (wrong results)
+    import ctypes
+    for mode, name in ((1, "tiles_ms_no_scatter"), (2, "tiles_ms_no_mma")):
+        N.load().n2v2r__debug_sparse_mode(ctypes.c_int(mode))
+        out[name] = timed(Lt)[0]
+    N.load().n2v2r__debug_sparse_mode(ctypes.c_int(0))
 if not only_tiles:
     Lp = D.make_layer(f32, storage="planes")
     del f32
