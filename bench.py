@@ -72,7 +72,7 @@ def parse_args():
                          "expanded in shared memory for sparse layers; auto = the product default")
     ap.add_argument("--no-cross-check", action="store_true",
                     help="skip the untimed second solve (other seed, l = 80) whose subspace angle against the timed solve is reported")
-    ap.add_argument("--seed-batch", type=int, default=16,
+    ap.add_argument("--seed-batch", type=int, default=3,
                     help="workload c5: solves that run concurrently and share every pass over a layer (1 = one after the other)")
     ap.add_argument("--cpu-ladder", default="2000,4000,8000",
                     help="--impl reference: node counts the reference path is timed at (all layers), ascending")

@@ -37,13 +37,27 @@ __device__ __forceinline__ float e4m3_to_float(uint8_t b) {
 __device__ __forceinline__ uint8_t float_to_e4m3(float x) { return (uint8_t)__nv_cvt_float_to_fp8(x, __NV_SATFINITE, __NV_E4M3); }
 
 // ---- operand: column maxima, then the six-term split -------------------------------------------------
-__global__ void __launch_bounds__(256) colmax_kernel(const float* __restrict__ X, int64_t n, int l, uint32_t* __restrict__ colmax_bits) {
+// stage 1: per-CTA column maxima of |X| (no atomics: part[cta][col]); stage 2 (colmax_final_kernel): maximum over the CTAs
+__global__ void __launch_bounds__(256) colmax_kernel(const float* __restrict__ X, int64_t n, int l, float* __restrict__ part) {
+  __shared__ float sm[256];
   const int rpb = 256 / l;
-  if ((int)threadIdx.x >= rpb * l) return;
   const int col = threadIdx.x % l, r = threadIdx.x / l;
   float m = 0.f;
-  for (int64_t row = (int64_t)blockIdx.x * rpb + r; row < n; row += (int64_t)gridDim.x * rpb) m = fmaxf(m, fabsf(X[row * l + col]));
-  if (m > 0.f) atomicMax(&colmax_bits[col], __float_as_uint(m));       // non-negative floats order like their bit patterns
+  if (r < rpb)
+    for (int64_t row = (int64_t)blockIdx.x * rpb + r; row < n; row += (int64_t)gridDim.x * rpb) m = fmaxf(m, fabsf(X[row * l + col]));
+  sm[threadIdx.x] = m;
+  __syncthreads();
+  if ((int)threadIdx.x < l) {
+    for (int rr = 1; rr < rpb; ++rr) m = fmaxf(m, sm[rr * l + threadIdx.x]);
+    part[(size_t)blockIdx.x * l + threadIdx.x] = m;
+  }
+}
+__global__ void __launch_bounds__(128) colmax_final_kernel(const float* __restrict__ part, int n_parts, int l, uint32_t* __restrict__ colmax_bits) {
+  const int col = threadIdx.x;
+  if (col >= l) return;
+  float m = 0.f;
+  for (int p = 0; p < n_parts; ++p) m = fmaxf(m, part[(size_t)p * l + col]);
+  colmax_bits[col] = __float_as_uint(m);
 }
 
 // X fp32 [n][l] -> Xs e4m3 [6][l][n_pad] (K-major operand), inv_scale[c] = 1 / s_c
@@ -242,9 +256,13 @@ int stream_apply_e4m3(cudaStream_t s, const StreamPlan& plan, const void* plane8
   uint8_t* xs8 = (uint8_t*)xs_ws;
   uint32_t* colmax = (uint32_t*)(xs8 + align_up((size_t)6 * l * n_pad));
   float* inv_scale = (float*)(colmax + 128);
-  N2V2R_REQUIRE(align_up((size_t)6 * l * n_pad) + 1024 <= plan.xs_bytes, "e4m3 product: operand workspace too small");
-  N2V2R_CUDA(cudaMemsetAsync(colmax, 0, sizeof(uint32_t) * l, s));
-  colmax_kernel<<<sm_count() * 4, 256, 0, s>>>(x, plan.n, l, colmax);
+  float* cm_part = inv_scale + 128;                       // [kColmaxCtas][l]
+  constexpr int kColmaxCtas = 96;
+  N2V2R_REQUIRE(align_up((size_t)6 * l * n_pad) + 1024 + sizeof(float) * kColmaxCtas * 80 <= plan.xs_bytes,
+                "e4m3 product: operand workspace too small");
+  colmax_kernel<<<kColmaxCtas, 256, 0, s>>>(x, plan.n, l, cm_part);
+  N2V2R_CHECK_LAUNCH();
+  colmax_final_kernel<<<1, 128, 0, s>>>(cm_part, kColmaxCtas, l, colmax);
   N2V2R_CHECK_LAUNCH();
   dim3 g2((unsigned)((n_pad + 31) / 32), (unsigned)((l + 31) / 32));
   split8_transpose_kernel<<<g2, 256, 0, s>>>(x, plan.n, l, n_pad, colmax, xs8, inv_scale);

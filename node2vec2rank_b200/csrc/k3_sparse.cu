@@ -284,7 +284,8 @@ struct SparseArgs {
   uint32_t a_plane_bytes, a_stage_bytes, x_bytes;
   uint32_t off_x, off_land, off_undo;  // byte offsets from the 1024-aligned base (A stages start at 0)
   uint32_t tmem_cols;
-  int debug_mode;                      // profiling only (n2v2r__debug_sparse_mode): 1 = no scatter / restore, 2 = no MMA issue
+  int debug_mode;                      // profiling only (n2v2r__debug_sparse_mode): 1 = no scatter / restore, 2 = no MMA issue, 3 = neither
+  unsigned long long* debug_clk;       // profiling only: per-CTA cycle counters of the pipeline roles (16 per CTA) or null
   const uint32_t* tile_ptr;
   const uint2* entries;
   float* out;
@@ -344,20 +345,27 @@ __global__ void __launch_bounds__(384, 1) sparse_mma_kernel(const __grid_constan
   } else if (warp == 1) {
     // ===== MMA issuer =====
     int as = 0, xs = 0; uint32_t pa = 0, px = 0, uphase = 0;
+    unsigned long long dbg[3] = {0, 0, 0};
     for (int u = blockIdx.x; u < n_units; u += gridDim.x) {
       const int split = u / a.n_tiles;
       const int kb0 = split * a.kb_per_split, kb1 = min(a.n_kb, kb0 + a.kb_per_split);
+      const long long ct0 = clock64();
       mbar_wait(bar_tempty, uphase ^ 1u);              // epilogue has drained the accumulators
+      dbg[2] += clock64() - ct0;
       tc_fence_after();
       bool first = true;
       for (int kb = kb0; kb < kb1; ++kb) {
+        const long long c0 = clock64();
         mbar_wait(bar_afull + 8 * as, pa);
+        const long long c1 = clock64();
         mbar_wait(bar_xfull + 8 * xs, px);
+        const long long c2 = clock64();
+        if (a.debug_clk && lane == 0) { dbg[0] += c1 - c0; dbg[1] += c2 - c1; }
         tc_fence_after();
         if (lane == 0) {
           const uint32_t abase0 = smem0 + as * a.a_stage_bytes;
           const uint32_t xbase = smem0 + a.off_x + xs * a.x_bytes;
-          for (int h = 0; h < (a.debug_mode == 2 ? 0 : a.mh); ++h) {
+          for (int h = 0; h < ((a.debug_mode & 2) ? 0 : a.mh); ++h) {
             bool acc = !first;
             for (int p = 0; p < a.n_planes; ++p) {
               const uint32_t idesc = idesc_bf16((3 - p) * a.l);
@@ -381,6 +389,7 @@ __global__ void __launch_bounds__(384, 1) sparse_mma_kernel(const __grid_constan
       __syncwarp();
       uphase ^= 1u;
     }
+    if (a.debug_clk && lane == 0) { for (int i = 0; i < 3; ++i) a.debug_clk[blockIdx.x * 16 + i] = dbg[i]; }
   } else if (warp == 2) {
     // ===== producer of the entry lists =====
     int ls = 0; uint32_t pl = 0;
@@ -465,6 +474,7 @@ __global__ void __launch_bounds__(384, 1) sparse_mma_kernel(const __grid_constan
     const int ct = threadIdx.x - 256;                  // 0..127
     int as = 0, ls = 0; uint32_t pa = 0, pl = 0;
     uint32_t prev0 = 0, prev1 = 0, prev2 = 0, prev3 = 0;   // entries scattered into each A stage by its previous use
+    unsigned long long dbg[6] = {0, 0, 0, 0, 0, 0};
     for (int u = blockIdx.x; u < n_units; u += gridDim.x) {
       const int split = u / a.n_tiles;
       const int kb0 = split * a.kb_per_split, kb1 = min(a.n_kb, kb0 + a.kb_per_split);
@@ -472,8 +482,10 @@ __global__ void __launch_bounds__(384, 1) sparse_mma_kernel(const __grid_constan
         const uint32_t abase = smem0 + as * a.a_stage_bytes;
         const uint32_t undo = smem0 + a.off_undo + as * (kUndoCap * 2);
         const uint32_t prev = as == 0 ? prev0 : as == 1 ? prev1 : as == 2 ? prev2 : prev3;
+        const long long c0 = clock64();
         mbar_wait(bar_aempty + 8 * as, pa ^ 1u);        // the MMAs that read this stage have retired
-        if (a.debug_mode == 1) {
+        const long long c1 = clock64();
+        if (a.debug_mode & 1) {
         } else if (prev > (uint32_t)kUndoCap) {
           for (uint32_t i = ct; i < (a.a_stage_bytes >> 4); i += 128) st_shared_zero16(abase + (i << 4));
         } else {
@@ -486,14 +498,19 @@ __global__ void __launch_bounds__(384, 1) sparse_mma_kernel(const __grid_constan
             }
           }
         }
+        const long long c2 = clock64();
         asm volatile("bar.sync 1, 128;" ::: "memory");  // every restore precedes every new entry
+        const long long c3 = clock64();
+        long long wl = 0;
         uint32_t total = 0;
         while (true) {
+          const long long w0 = clock64();
           mbar_wait(bar_lfull + 8 * ls, pl);
+          wl += clock64() - w0;
           const uint32_t c = lcnt[ls];
           const uint32_t nent = c & 0x7fffffffu;
           const uint32_t land = smem0 + a.off_land + ls * (kLandCap * 8);
-          for (uint32_t j = ct; j < (a.debug_mode == 1 ? 0u : nent); j += 128) {
+          for (uint32_t j = ct; j < ((a.debug_mode & 1) ? 0u : nent); j += 128) {
             const uint2 ent = ld_shared_v2(land + 8 * j);
             const uint32_t pos = ent.x & 0xFFFFu;
             if (total + j < (uint32_t)kUndoCap) st_shared_u16(undo + 2 * (total + j), pos);
@@ -509,11 +526,17 @@ __global__ void __launch_bounds__(384, 1) sparse_mma_kernel(const __grid_constan
           if (c & 0x80000000u) break;
         }
         if (as == 0) prev0 = total; else if (as == 1) prev1 = total; else if (as == 2) prev2 = total; else prev3 = total;
+        const long long c4 = clock64();
         fence_proxy_async();                            // generic-proxy stores -> visible to the tensor core's async proxy
         mbar_arrive(bar_afull + 8 * as);
+        if (a.debug_clk) {
+          const long long c5 = clock64();
+          dbg[0] += c1 - c0; dbg[1] += c2 - c1; dbg[2] += c3 - c2; dbg[3] += wl; dbg[4] += (c4 - c3) - wl; dbg[5] += c5 - c4;
+        }
         if (++as == a.a_stages) { as = 0; pa ^= 1u; }
       }
     }
+    if (a.debug_clk && ct == 0) { for (int i = 0; i < 6; ++i) a.debug_clk[blockIdx.x * 16 + 4 + i] = dbg[i]; }
   }
   tc_fence_before();
   __syncthreads();
@@ -525,6 +548,7 @@ __global__ void __launch_bounds__(384, 1) sparse_mma_kernel(const __grid_constan
 
 // ---- host ---------------------------------------------------------------------------------------
 static int g_sparse_debug_mode = 0;
+static unsigned long long* g_sparse_debug_clk = nullptr;
 // K split that balances (row tiles x splits) units over the persistent CTAs
 static int pick_splits(int n_tiles, int n_kb, int max_splits, int grid) {
   int best = 1;
@@ -593,6 +617,7 @@ int stream_apply_tiles(cudaStream_t s, const StreamPlan& plan, const uint32_t* t
   a.out_ld = plan.l;
   a.split_stride = rows_pad * plan.l;
   a.debug_mode = g_sparse_debug_mode;
+  a.debug_clk = g_sparse_debug_clk;
   a.tile_ptr = tile_ptr;
   a.entries = (const uint2*)entries;
   a.out = parts;
@@ -627,6 +652,7 @@ using namespace n2v2r;
 
 // profiling hook (not part of the ABI header): skip parts of the sparse product kernel to time the rest
 extern "C" void n2v2r__debug_sparse_mode(int mode) { g_sparse_debug_mode = mode; }
+extern "C" void n2v2r__debug_sparse_clk(void* d_buf) { g_sparse_debug_clk = (unsigned long long*)d_buf; }
 
 // ---- C ABI: building the compressed tiles --------------------------------------------------------
 extern "C" int n2v2r_tiles_count(void* stream, const float* d_in, int64_t n, int64_t ld, uint32_t* d_counts, uint32_t* d_counts_t,

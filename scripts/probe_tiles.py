@@ -42,9 +42,18 @@ ms_t, y_t = timed(Lt)
 out["tiles_ms"] = ms_t
 if "--debug-modes" in sys.argv:                 # profiling: the kernel without its converters / without its MMAs (wrong results)
     import ctypes
-    for mode, name in ((1, "tiles_ms_no_scatter"), (2, "tiles_ms_no_mma")):
+    names = ["mma:wait_a_full", "mma:wait_x_full", "mma:wait_tmem_empty", "-", "conv:wait_a_empty", "conv:restore", "conv:bar", "conv:wait_landing",
+             "conv:scatter", "conv:fence+arrive"]
+    for mode, name in ((0, "full"), (1, "no_scatter"), (2, "no_mma"), (3, "skeleton")):
         N.load().n2v2r__debug_sparse_mode(ctypes.c_int(mode))
-        out[name] = timed(Lt)[0]
+        out[f"tiles_ms_{name}"] = timed(Lt)[0]
+        clk = torch.zeros(148 * 16, dtype=torch.int64, device=dev)
+        N.load().n2v2r__debug_sparse_clk(ctypes.c_void_p(clk.data_ptr()))
+        D.layer_apply(Lt, x, ws=ws)
+        torch.cuda.synchronize()
+        N.load().n2v2r__debug_sparse_clk(ctypes.c_void_p(0))
+        c = clk.view(148, 16).double().mean(dim=0).cpu().numpy()
+        out[f"cycles_{name}"] = {nm: round(float(v)) for nm, v in zip(names, c) if nm != "-"}
     N.load().n2v2r__debug_sparse_mode(ctypes.c_int(0))
 if not only_tiles:
     Lp = D.make_layer(f32, storage="planes")
