@@ -127,7 +127,8 @@ int n2v2r_transpose_planes(void* stream, const void* d_planes, int n_planes, int
  *     { u16 pos, bf16 p0, bf16 p1, bf16 p2 },   value = p0 + p1 + p2 (exact fp32),
  * pos = element offset of (r, c) inside a K-major SWIZZLE_128B bf16 tile:
  *     pos = (r>>3)*512 + (r&7)*64 + (((c>>3) ^ (r&7))<<3) + (c&7);
- * lists are padded to an even number of entries with pos = 0xFFFF; d_tile_ptr[t] is the first entry of tile t,
+ * lists are padded to a multiple of 4 entries with pos = 0xFFFF and hold their entries in the order the product kernel's
+ * converter warps want (shared-memory-bank interleaved); d_tile_ptr[t] is the first entry of tile t,
  * d_tile_ptr[n_tiles] the total.  Build: count (non-zeros per 128-row tile of A and of A^T, planes the values
  * need, symmetry; synchronises) -> scan (tile_rows chosen by the caller; synchronises, returns the number of
  * entries to allocate) -> fill (transpose=1 writes the tiles of A^T from the same dense input).

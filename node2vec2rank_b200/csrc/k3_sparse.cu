@@ -26,7 +26,7 @@ namespace n2v2r {
 constexpr int kLandCap = 512;        // entries per landing slot (4 KB)
 constexpr int kUndoCap = 2048;       // positions remembered per A stage; a denser tile pair is cleared as a whole
 constexpr int kSortCap = 2048;        // tile lists up to this length are written in bank-interleaved order (builder)
-constexpr uint32_t kPosSkip = 0xFFFFu;   // padding entry (tile lists are padded to an even number of entries)
+constexpr uint32_t kPosSkip = 0xFFFFu;   // padding entry (tile lists are padded to a multiple of 4 entries = 32 bytes)
 
 // element offset of (row r, column c) inside one K-major SWIZZLE_128B plane of a (tile_rows x 64) bf16 tile
 __host__ __device__ __forceinline__ uint32_t swz_pos(int r, int c) {
@@ -56,6 +56,14 @@ __device__ __forceinline__ uint2 ld_shared_v2(uint32_t addr) {
   uint2 v;
   asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
   return v;
+}
+__device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void st_shared_v2(uint32_t addr, uint32_t a, uint32_t b) {
+  asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(addr), "r"(a), "r"(b) : "memory");
 }
 __device__ __forceinline__ void st_shared_zero16(uint32_t addr) {
   asm volatile("st.shared.v4.u32 [%0], {%1, %1, %1, %1};" ::"r"(addr), "r"(0u) : "memory");
@@ -142,7 +150,7 @@ __global__ void __launch_bounds__(1024) tiles_scan_kernel(const uint32_t* __rest
       const int r128 = rt * mh + h;
       if (r128 < n_rt128) c += cnt128[(size_t)r128 * n_kb + kb];
     }
-    return (c + 1u) & ~1u;
+    return (c + 3u) & ~3u;
   };
   unsigned long long s = 0;
   for (int64_t t = b; t < e; ++t) s += count_of(t);
@@ -164,6 +172,16 @@ __global__ void __launch_bounds__(1024) tiles_scan_kernel(const uint32_t* __rest
     tile_ptr[n_tiles] = (uint32_t)part[1023];
     *total = part[1023];
   }
+}
+
+// A converter thread of the product kernel handles 4 consecutive entries (one 32-byte load) and issues its j-th scatter store
+// for entry 4 b + j of a block of 128 (b = its lane): so the bank-interleaved order i = 32 j + b (32 different banks per round
+// j) is stored transposed, position 4 b + j.  A shorter last block of m entries (m % 4 == 0) uses the same rule with m / 4 lanes.
+__device__ __forceinline__ uint32_t converter_slot(uint32_t slot, uint32_t total4) {
+  const uint32_t b0 = slot & ~127u;
+  const uint32_t m = (total4 - b0 < 128u) ? total4 - b0 : 128u;
+  const uint32_t q = m >> 2, s_ = slot - b0;
+  return b0 + 4u * (s_ % q) + s_ / q;
 }
 
 // One CTA per (tile, k block) of the TARGET matrix B (B = A, or B = A^T when TRANS): compacts the non-zeros of the tile in a
@@ -210,6 +228,7 @@ __global__ void __launch_bounds__(256) tiles_fill_kernel(const float* __restrict
   // shared-memory bank b goes to slot (j, b), so that the 32 lanes of a converter warp, which scatter 32 consecutive
   // entries with one store instruction, hit 32 different banks (a random order costs ~6 conflict wavefronts per store).
   const bool sorted = total <= (uint32_t)kSortCap;
+  const uint32_t total4 = (total + 3u) & ~3u;              // lists are padded to a multiple of 4 entries (32 bytes) with skip entries
   const uint32_t lt = (1u << lane) - 1u;
 #pragma unroll
   for (int j = 0; j < RPW; ++j) {
@@ -244,10 +263,12 @@ __global__ void __launch_bounds__(256) tiles_fill_kernel(const float* __restrict
         slot += cb < rk ? cb : rk;                                   // complete rounds before mine
         slot += (bb < bank && cb > rk) ? 1u : 0u;                    // banks ahead of mine in my round
       }
-      entries[(size_t)tile_base + slot] = stage[i];
+      entries[(size_t)tile_base + converter_slot(slot, total4)] = stage[i];
     }
+    for (uint32_t i = total + threadIdx.x; i < total4; i += 256) entries[(size_t)tile_base + converter_slot(i, total4)] = make_uint2(kPosSkip, 0u);
+  } else {
+    for (uint32_t i = total + threadIdx.x; i < total4; i += 256) entries[(size_t)tile_base + i] = make_uint2(kPosSkip, 0u);
   }
-  if (threadIdx.x == 0 && (total & 1u)) entries[(size_t)tile_base + total] = make_uint2(kPosSkip, 0u);
 }
 
 // test / to_dense helper: out[(rt*TR + r) * ld + kb*64 + c] = p0 + p1 + p2 (out zero-filled by the caller)
@@ -489,12 +510,16 @@ __global__ void __launch_bounds__(384, 1) sparse_mma_kernel(const __grid_constan
         } else if (prev > (uint32_t)kUndoCap) {
           for (uint32_t i = ct; i < (a.a_stage_bytes >> 4); i += 128) st_shared_zero16(abase + (i << 4));
         } else {
-          for (uint32_t i = ct; i < prev; i += 128) {
-            const uint32_t pos = ld_shared_u16(undo + 2 * i);
-            if (pos != kPosSkip) {
-              st_shared_u16(abase + 2 * pos, 0u);
-              if (a.n_planes > 1) st_shared_u16(abase + a.a_plane_bytes + 2 * pos, 0u);
-              if (a.n_planes > 2) st_shared_u16(abase + 2 * a.a_plane_bytes + 2 * pos, 0u);
+          for (uint32_t i = 4 * ct; i < prev; i += 512) {        // 4 remembered positions per thread and round: one 8-byte load
+            const uint2 pp = ld_shared_v2(undo + 2 * i);
+            const uint32_t ps[4] = {pp.x & 0xFFFFu, pp.x >> 16, pp.y & 0xFFFFu, pp.y >> 16};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              if (ps[e] != kPosSkip) {
+                st_shared_u16(abase + 2 * ps[e], 0u);
+                if (a.n_planes > 1) st_shared_u16(abase + a.a_plane_bytes + 2 * ps[e], 0u);
+                if (a.n_planes > 2) st_shared_u16(abase + 2 * a.a_plane_bytes + 2 * ps[e], 0u);
+              }
             }
           }
         }
@@ -508,16 +533,22 @@ __global__ void __launch_bounds__(384, 1) sparse_mma_kernel(const __grid_constan
           mbar_wait(bar_lfull + 8 * ls, pl);
           wl += clock64() - w0;
           const uint32_t c = lcnt[ls];
-          const uint32_t nent = c & 0x7fffffffu;
+          const uint32_t nent = c & 0x7fffffffu;         // a multiple of 4, at most kLandCap = 4 x 128
           const uint32_t land = smem0 + a.off_land + ls * (kLandCap * 8);
-          for (uint32_t j = ct; j < ((a.debug_mode & 1) ? 0u : nent); j += 128) {
-            const uint2 ent = ld_shared_v2(land + 8 * j);
-            const uint32_t pos = ent.x & 0xFFFFu;
-            if (total + j < (uint32_t)kUndoCap) st_shared_u16(undo + 2 * (total + j), pos);
-            if (pos != kPosSkip) {
-              st_shared_u16(abase + 2 * pos, ent.x >> 16);
-              if (a.n_planes > 1) st_shared_u16(abase + a.a_plane_bytes + 2 * pos, ent.y & 0xFFFFu);
-              if (a.n_planes > 2) st_shared_u16(abase + 2 * a.a_plane_bytes + 2 * pos, ent.y >> 16);
+          const uint32_t j = 4 * ct;
+          if (!(a.debug_mode & 1) && j < nent) {         // this thread's 4 entries of the chunk: one 32-byte load
+            const uint4 e01 = ld_shared_v4(land + 8 * j), e23 = ld_shared_v4(land + 8 * j + 16);
+            const uint32_t ex[4] = {e01.x, e01.z, e23.x, e23.z}, ey[4] = {e01.y, e01.w, e23.y, e23.w};
+            if (total + j < (uint32_t)kUndoCap)
+              st_shared_v2(undo + 2 * (total + j), (ex[0] & 0xFFFFu) | (ex[1] << 16), (ex[2] & 0xFFFFu) | (ex[3] << 16));
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const uint32_t pos = ex[e] & 0xFFFFu;
+              if (pos != kPosSkip) {
+                st_shared_u16(abase + 2 * pos, ex[e] >> 16);
+                if (a.n_planes > 1) st_shared_u16(abase + a.a_plane_bytes + 2 * pos, ey[e] & 0xFFFFu);
+                if (a.n_planes > 2) st_shared_u16(abase + 2 * a.a_plane_bytes + 2 * pos, ey[e] >> 16);
+              }
             }
           }
           mbar_arrive(bar_lempty + 8 * ls);

@@ -80,12 +80,13 @@ def test_projection_vs_fp64(gpu, shape):
         ref = port.bipartite_to_unipartite_projection(W, on)
         assert out.shape == ref.shape and out.dtype == np.float32
         assert np.abs(out - ref).max() <= 4e-6 * np.abs(ref).max()
-        # per entry: |out - ref| <= c eps32 sum_k |w||w| (the bound of an fp32 dot product; the float32 cast of the reference's
+        # per entry: |out - ref| <= c eps32 sum_k |w||w| with c = 64 (measured 17-21: the tensor core's fp32 adder truncates, over
+        # chains of 512 products; the worst case of a plain fp32 dot product is K eps32, the float32 cast of the reference's
         # float64 product alone costs eps32/2 |ref|)
         Wa = np.abs(W)
         bound = (Wa.T @ Wa) if on.casefold() == "columns" else (Wa @ Wa.T)
         ratio = float((np.abs(out.astype(np.float64) - ref) / (np.finfo(np.float32).eps * bound)).max())
-        assert ratio <= 16.0, (shape, on, ratio)
+        assert ratio <= 64.0, (shape, on, ratio)
         assert np.array_equal(out, out.T)
     with pytest.raises(ValueError):
         bipartite_to_unipartite_projection(W, "diagonal")

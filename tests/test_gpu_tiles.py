@@ -37,11 +37,11 @@ def test_tiles_round_trip(gpu, n, density, planes, symmetric):
     assert P == (planes if nnz else 1) and L.n_planes == P
     assert sym == bool(np.array_equal(a, a.T)) and L.symmetric == sym
     assert L.tile_rows == (256 if P <= 2 else 128)
-    # every list is padded to an even length: between nnz and nnz + number of tiles
+    # every list is padded to a multiple of 4 entries: between nnz and nnz + 3 x number of tiles
     n_tiles = L.tile_ptr.numel() - 1
-    assert nnz <= L.n_entries <= nnz + n_tiles and L.n_entries % 2 == 0 and L.entries.shape[0] >= L.n_entries
+    assert nnz <= L.n_entries <= nnz + 3 * n_tiles and L.n_entries % 4 == 0 and L.entries.shape[0] >= L.n_entries
     tp = L.tile_ptr.cpu().numpy().astype(np.int64)
-    assert tp[0] == 0 and np.all(np.diff(tp) >= 0) and np.all(tp % 2 == 0) and tp[-1] == L.n_entries
+    assert tp[0] == 0 and np.all(np.diff(tp) >= 0) and np.all(tp % 4 == 0) and tp[-1] == L.n_entries
     assert np.array_equal(L.numpy().view(np.uint32), a.view(np.uint32))
     if not sym:
         assert L.tile_ptr_t is not None
