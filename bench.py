@@ -432,7 +432,8 @@ def transfer_note(x):
     """How the host graphs crossed PCIe in the e2e leg (device.layers_from_host.last_stats)."""
     if not x or not x.get("packed_chunks"):
         return "dense float32 copies"
-    return (f"packed on the host ({x['packed_chunks']} row chunks as bitmap + non-zero values, {x['dense_chunks']} dense; "
+    return (f"packed on the host ({x['packed_chunks']} row chunks as bitmap + non-zero values, {x['dense_chunks']} dense"
+            + (" on a second copy stream while the host cores pack" if x.get("hybrid") else "") + "; "
             f"{x.get('threads', 0)} host threads, {x.get('pack_s', 0):.3f} s packing of {x.get('total_s', 0):.3f} s transfer + load pass), "
             f"expanded on the device")
 

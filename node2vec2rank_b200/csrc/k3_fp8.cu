@@ -20,13 +20,17 @@
 
 namespace n2v2r {
 
+// fill = 1: the A tile stays in the collector buffer for the next MMA; fill = 0: it is taken from there (last use)
+template <int FILL>
 __device__ __forceinline__ void umma_f8(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f8f6f4 [%0], %1, %2, %3, p;\n\t}"
-      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-      : "memory");
+  if (FILL)
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f8f6f4.collector::a::fill [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+  else
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f8f6f4.collector::a::lastuse [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
 // kind::f8f6f4 instruction descriptor: D = f32, A = B = e4m3 (format code 0), both K-major, M = 128
 __device__ __forceinline__ uint32_t idesc_e4m3(int N) { return (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((128u >> 4) << 24); }
@@ -189,8 +193,9 @@ __global__ void __launch_bounds__(192, 1) stream_mma8_kernel(const __grid_consta
 #pragma unroll
           for (int k = 0; k < 4; ++k) {                    // K = 32 e4m3 elements = 32 bytes per instruction
             const uint32_t acc = (first && k == 0) ? 0u : 1u;
-            umma_f8(tmem_base, sw128_desc(abase + k * 32), sw128_desc(xbase + k * 32), idesc, acc);                       // terms 0..2
-            umma_f8(tmem_base + n3, sw128_desc(abase + k * 32), sw128_desc(xbase + n3 * 128 + k * 32), idesc, acc);       // terms 3..5
+            // both term groups meet the same A k-slice: read from shared memory once, kept in the collector for the second MMA
+            umma_f8<1>(tmem_base, sw128_desc(abase + k * 32), sw128_desc(xbase + k * 32), idesc, acc);                    // terms 0..2
+            umma_f8<0>(tmem_base + n3, sw128_desc(abase + k * 32), sw128_desc(xbase + n3 * 128 + k * 32), idesc, acc);    // terms 3..5
           }
           umma_commit(bar_empty + 8 * stage);
         }

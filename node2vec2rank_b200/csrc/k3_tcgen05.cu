@@ -100,7 +100,7 @@ __global__ void __launch_bounds__(192, 1) stream_mma_kernel(const __grid_constan
         if (lane == 0) {
           const uint32_t base = smem0 + stage * a.stage_bytes;
           const uint32_t xbase = base + a.n_planes * a.a_plane_bytes;
-          for (int bk = 0; bk < a.nb; ++bk) {
+          if (a.nb == 1) {
             for (int h = 0; h < a.mh; ++h) {
               bool acc = !first;
               for (int p = 0; p < a.n_planes; ++p) {
@@ -108,10 +108,27 @@ __global__ void __launch_bounds__(192, 1) stream_mma_kernel(const __grid_constan
                 const uint32_t abase = base + p * a.a_plane_bytes + h * 16384;
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
-                  umma_bf16(tmem_base + (bk * a.mh + h) * nacc, sw128_desc(abase + k * 32), sw128_desc(xbase + bk * a.x_bytes + k * 32),
-                            idesc, acc ? 1u : 0u);
+                  umma_bf16(tmem_base + h * nacc, sw128_desc(abase + k * 32), sw128_desc(xbase + k * 32), idesc, acc ? 1u : 0u);
                   acc = true;
                 }
+              }
+            }
+          } else {
+            // seed batching (mh == 1): the nb operand blocks meet the same A k-slice back to back; it is read from shared memory
+            // by the first MMA (collector fill) and taken from the collector buffer by the others
+            for (int p = 0; p < a.n_planes; ++p) {
+              const uint32_t idesc = idesc_bf16((3 - p) * a.l);
+              const uint32_t abase = base + p * a.a_plane_bytes;
+              const uint32_t acc0 = (first && p == 0) ? 0u : 1u;
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                const uint32_t acc = k == 0 ? acc0 : 1u;
+                const uint64_t ad = sw128_desc(abase + k * 32);
+                umma_bf16_collector(tmem_base, ad, sw128_desc(xbase + k * 32), idesc, acc, kCollectorFill);
+                if (a.nb == 3)
+                  umma_bf16_collector(tmem_base + nacc, ad, sw128_desc(xbase + a.x_bytes + k * 32), idesc, acc, kCollectorUse);
+                umma_bf16_collector(tmem_base + (a.nb - 1) * nacc, ad, sw128_desc(xbase + (a.nb - 1) * a.x_bytes + k * 32), idesc, acc,
+                                    kCollectorLastUse);
               }
             }
           }

@@ -54,6 +54,21 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint6
       ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// The same with the A-operand collector: FILL keeps the A tile in the tensor core's collector buffer after this MMA, USE / LASTUSE
+// take it from there instead of reading shared memory again (consecutive MMAs of one A tile against different B tiles).
+enum { kCollectorNone = 0, kCollectorFill = 1, kCollectorUse = 2, kCollectorLastUse = 3 };
+__device__ __forceinline__ void umma_bf16_collector(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate,
+                                                    int usage) {
+#define N2V2R_UMMA_BF16(Q)                                                                        \
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"                                 \
+               "tcgen05.mma.cta_group::1.kind::f16" Q " [%0], %1, %2, %3, p;\n\t}"                \
+               ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory")
+  if (usage == kCollectorFill) N2V2R_UMMA_BF16(".collector::a::fill");
+  else if (usage == kCollectorUse) N2V2R_UMMA_BF16(".collector::a::use");
+  else if (usage == kCollectorLastUse) N2V2R_UMMA_BF16(".collector::a::lastuse");
+  else N2V2R_UMMA_BF16("");
+#undef N2V2R_UMMA_BF16
+}
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }

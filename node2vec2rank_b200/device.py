@@ -386,6 +386,9 @@ def make_layer(x32: torch.Tensor, n_planes=None, colsum=None, check_symmetry=Tru
 PACK_MIN_ENTRIES = 4_000_000          # below this a layer crosses PCIe dense (the packed pipeline has fixed costs)
 PACK_CHUNK_ENTRIES = 300_000_000      # rows are packed and copied in chunks of about this many entries
 PACK_MAX_DENSITY = 0.3                # staging capacity for the non-zero values, as a fraction of a chunk's entries
+PACK_DENSE_EVERY = 4                  # pinned sources: every 4th row chunk crosses PCIe dense on its own stream while the host
+                                      # cores pack the others (packing runs at ~150 GB/s of host reads, the otherwise idle copy
+                                      # engine adds ~55 GB/s); 0 = pack every chunk
 _pack_staging = {}                    # (chunk_rows, cols) -> two pinned staging slots, kept across calls (pinning is slow)
 
 
@@ -455,12 +458,16 @@ def _layers_from_host_packed(srcs, n_planes, chunk_rows, slots, storage="auto"):
     words = (cols + 31) // 32
     cur = torch.cuda.current_stream(dev)
     copy = torch.cuda.Stream(dev)
+    copy2 = torch.cuda.Stream(dev)                        # dense chunks of the hybrid transfer
+    hybrid = PACK_DENSE_EVERY > 1 and all(x.is_pinned() for x in srcs) and -(-rows // chunk_rows) >= PACK_DENSE_EVERY
     dense = [torch.empty((rows, cols), dtype=torch.float32, device=dev) for _ in range(min(2, len(srcs)))]
     twins = [{k: torch.empty_like(v, device=dev) for k, v in slot.items()} for slot in slots]
     copy.wait_stream(cur)                                 # the buffers were allocated on the current stream
+    copy2.wait_stream(cur)
     ready, consumed = queue.Queue(), queue.Queue()
     threads = host_threads()
     stats = dict(packed_chunks=0, dense_chunks=0, h2d_bytes=0, pack_s=0.0, producer_s=0.0, total_s=0.0, threads=threads)
+    stats["hybrid"] = bool(hybrid)
     t_begin = time.perf_counter()
 
     def produce():
@@ -475,10 +482,21 @@ def _layers_from_host_packed(srcs, n_planes, chunk_rows, slots, storage="auto"):
                         if done is None:                  # the consumer failed
                             return
                         copy.wait_event(done)
+                        copy2.wait_event(done)
                     out = dense[t % 2]
-                    for r0 in range(0, rows, chunk_rows):
+                    if hybrid and not dense_mode:         # queue this layer's dense chunks first: the copy engine starts at once
+                        with torch.cuda.stream(copy2):
+                            for ci, r0 in enumerate(range(0, rows, chunk_rows)):
+                                if ci % PACK_DENSE_EVERY == PACK_DENSE_EVERY - 1:
+                                    r1 = min(rows, r0 + chunk_rows)
+                                    out[r0:r1].copy_(src[r0:r1], non_blocking=True)
+                                    stats["dense_chunks"] += 1
+                                    stats["h2d_bytes"] += (r1 - r0) * cols * 4
+                    for ci, r0 in enumerate(range(0, rows, chunk_rows)):
                         r1 = min(rows, r0 + chunk_rows)
                         nnz = C.c_int64(-1)
+                        if hybrid and not dense_mode and ci % PACK_DENSE_EVERY == PACK_DENSE_EVERY - 1:
+                            continue
                         if not dense_mode:
                             c = len(sent)
                             slot, twin = slots[c % 2], twins[c % 2]
@@ -507,6 +525,7 @@ def _layers_from_host_packed(srcs, n_planes, chunk_rows, slots, storage="auto"):
                                                           N.ptr(twin["row_start"]), r1 - r0, cols, N.ptr(out[r0:r1]), cols))
                         stats["packed_chunks"] += 1
                         stats["h2d_bytes"] += (r1 - r0) * (words * 4 + 8) + k * 4
+                    copy.wait_stream(copy2)
                     ev = torch.cuda.Event()
                     ev.record(copy)
                     ready.put(ev)
@@ -533,6 +552,7 @@ def _layers_from_host_packed(srcs, n_planes, chunk_rows, slots, storage="auto"):
         raise
     finally:
         worker.join()
+        cur.wait_stream(copy2)
         cur.wait_stream(copy)          # also on the error path: the buffers go back to the allocator only after the copy stream
     stats["total_s"] = time.perf_counter() - t_begin
     layers_from_host.last_stats = stats
