@@ -69,6 +69,55 @@ __device__ __forceinline__ void st_shared_zero16(uint32_t addr) {
   asm volatile("st.shared.v4.u32 [%0], {%1, %1, %1, %1};" ::"r"(addr), "r"(0u) : "memory");
 }
 
+// ---- CTA-pair (cta_group::2) helpers -------------------------------------------------------------------
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// arrive on the mbarrier at the same shared-memory offset in CTA `cta` of the cluster
+__device__ __forceinline__ void mbar_arrive_remote(uint32_t bar, uint32_t cta) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(bar), "r"(cta));
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(r) : "memory");
+}
+// wait on a local mbarrier whose arrivals come from the peer CTA (cluster-scope acquire)
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
+  uint32_t done = 0;
+  const long long t0 = clock64();
+  while (true) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (done) break;
+    if (clock64() - t0 > 4000000000ll) __trap();
+  }
+}
+__device__ __forceinline__ void umma_bf16_2cta(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// completion of the pair's MMAs -> the mbarrier at this offset in BOTH CTAs
+__device__ __forceinline__ void umma_commit_2cta(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(bar), "h"((unsigned short)3) : "memory");
+}
+// kind::f16 instruction descriptor of the pair MMA: M = 256 (128 rows per CTA)
+__device__ __forceinline__ uint32_t idesc_bf16_m256(int N) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((256u >> 4) << 24);
+}
+
 // =================================================================================================
 // Builder: dense fp32 (n x n, leading dimension ld) -> compressed tiles of A or of A^T
 // =================================================================================================
@@ -314,9 +363,17 @@ struct SparseArgs {
 
 // Warp roles (384 threads): 0 TMA producer of the split operand X, 1 TMEM owner + MMA issuer, 2 producer of the entry
 // lists (cp.async.bulk), 3 idle, 4-7 epilogue, 8-11 converters.
-__global__ void __launch_bounds__(384, 1) sparse_mma_kernel(const __grid_constant__ CUtensorMap mapX, const SparseArgs a) {
+//
+// CTA2 = true: two CTAs of a cluster (one TPC) work on two vertically adjacent row tiles as ONE tcgen05.mma.cta_group::2 of
+// M = 256: every CTA expands its own tile and holds only HALF of the split operand (the pair MMA takes N/2 operand rows from
+// each CTA), so the shared-memory operand traffic per SM -- the bound of this kernel: the tensor core reads its shared-memory
+// operands at ~64 B/clk -- drops from A + B to A + B/2.  CTA 0 issues the MMAs; warp 1 of CTA 1 forwards "my A stage and my
+// operand half are ready" to it; completion (tcgen05.commit ... multicast) releases the stages and the accumulators in both.
+template <bool CTA2>
+__global__ void __launch_bounds__(384, 1) sparse_mma_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUtensorMap mapX1,
+                                                            const __grid_constant__ CUtensorMap mapX2, const SparseArgs a) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bars[36];
+  __shared__ __align__(8) uint64_t bars[40];
   __shared__ uint32_t tmem_base_smem;
   __shared__ uint32_t lcnt[8];
   const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -325,53 +382,90 @@ __global__ void __launch_bounds__(384, 1) sparse_mma_kernel(const __grid_constan
   const uint32_t bar_afull = smem_u32(&bars[8]), bar_aempty = smem_u32(&bars[12]);
   const uint32_t bar_lfull = smem_u32(&bars[16]), bar_lempty = smem_u32(&bars[24]);
   const uint32_t bar_tfull = smem_u32(&bars[32]), bar_tempty = smem_u32(&bars[33]);
-  const int n_units = a.n_tiles * a.n_splits;
+  const uint32_t bar_pfull = smem_u32(&bars[34]);          // CTA2, leader: the peer's A stage + operand half are ready
+  const uint32_t cr = CTA2 ? cluster_ctarank() : 0u;       // rank in the CTA pair
+  const int cid = CTA2 ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int ncl = CTA2 ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  const int n_st = CTA2 ? (a.n_tiles + 1) >> 1 : a.n_tiles; // units walk (pair of) row tiles x K splits
+  const int n_units = n_st * a.n_splits;
   const int nacc = 3 * a.l;
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < a.x_stages; ++i) { mbar_init(bar_xfull + 8 * i, 1); mbar_init(bar_xempty + 8 * i, 1); }
-    for (int i = 0; i < a.a_stages; ++i) { mbar_init(bar_afull + 8 * i, 128); mbar_init(bar_aempty + 8 * i, 1); }
+    for (int i = 0; i < a.a_stages; ++i) { mbar_init(bar_afull + 8 * i, 128); mbar_init(bar_aempty + 8 * i, 1); mbar_init(bar_pfull + 8 * i, 1); }
     for (int i = 0; i < a.l_slots; ++i) { mbar_init(bar_lfull + 8 * i, 1); mbar_init(bar_lempty + 8 * i, 128); }
     mbar_init(bar_tfull, 1);
-    mbar_init(bar_tempty, 4);
+    mbar_init(bar_tempty, CTA2 ? 8 : 4);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_smem)), "r"(a.tmem_cols));
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    if (CTA2) {
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_smem)), "r"(a.tmem_cols));
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;");
+    } else {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_smem)), "r"(a.tmem_cols));
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
   }
   // every A stage starts as zeros; from then on the converters restore the zeros themselves
   for (uint32_t i = threadIdx.x; i < a.a_stages * (a.a_stage_bytes >> 4); i += blockDim.x) st_shared_zero16(smem0 + (i << 4));
   fence_proxy_async();
   tc_fence_before();
   __syncthreads();
+  if (CTA2) cluster_sync_all();                            // the peer's barriers exist before anything is signalled across
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_smem;
+  // CTA2: operand halves of this CTA per plane term group: rows [cr * nh, (cr + 1) * nh) of the first (3 - p) l operand rows
+  const int nh0 = 3 * a.l / 2, nh1 = a.l, nh2 = a.l / 2;
+  const uint32_t xoff1 = (uint32_t)nh0 * 128u, xoff2 = xoff1 + (uint32_t)nh1 * 128u;
 
   if (warp == 0) {
     // ===== TMA producer of the split operand =====
     if (lane == 0) {
       int xs = 0; uint32_t px = 0;
-      for (int u = blockIdx.x; u < n_units; u += gridDim.x) {
-        const int split = u / a.n_tiles;
+      for (int u = cid; u < n_units; u += ncl) {
+        const int split = u / n_st;
         const int kb0 = split * a.kb_per_split, kb1 = min(a.n_kb, kb0 + a.kb_per_split);
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(bar_xempty + 8 * xs, px ^ 1u);
           mbar_expect_tx(bar_xfull + 8 * xs, a.x_bytes);
-          tma_load_3d(&mapX, bar_xfull + 8 * xs, smem0 + a.off_x + xs * a.x_bytes, kb * 64, 0, 0);
+          const uint32_t xb = smem0 + a.off_x + xs * a.x_bytes;
+          if (CTA2) {
+            tma_load_2d(&mapX, bar_xfull + 8 * xs, xb, kb * 64, (int)cr * nh0);
+            if (a.n_planes > 1) tma_load_2d(&mapX1, bar_xfull + 8 * xs, xb + xoff1, kb * 64, (int)cr * nh1);
+            if (a.n_planes > 2) tma_load_2d(&mapX2, bar_xfull + 8 * xs, xb + xoff2, kb * 64, (int)cr * nh2);
+          } else {
+            tma_load_3d(&mapX, bar_xfull + 8 * xs, xb, kb * 64, 0, 0);
+          }
           if (++xs == a.x_stages) { xs = 0; px ^= 1u; }
         }
+      }
+    }
+  } else if (warp == 1 && CTA2 && cr == 1) {
+    // ===== CTA 1 of the pair: tell the issuing CTA when this CTA's A stage and operand half are ready =====
+    int as = 0, xs = 0; uint32_t pa = 0, px = 0;
+    for (int u = cid; u < n_units; u += ncl) {
+      const int split = u / n_st;
+      const int kb0 = split * a.kb_per_split, kb1 = min(a.n_kb, kb0 + a.kb_per_split);
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(bar_afull + 8 * as, pa);
+        mbar_wait(bar_xfull + 8 * xs, px);
+        if (lane == 0) mbar_arrive_remote(bar_pfull + 8 * as, 0);
+        __syncwarp();
+        if (++as == a.a_stages) { as = 0; pa ^= 1u; }
+        if (++xs == a.x_stages) { xs = 0; px ^= 1u; }
       }
     }
   } else if (warp == 1) {
     // ===== MMA issuer =====
     int as = 0, xs = 0; uint32_t pa = 0, px = 0, uphase = 0;
     unsigned long long dbg[3] = {0, 0, 0};
-    for (int u = blockIdx.x; u < n_units; u += gridDim.x) {
-      const int split = u / a.n_tiles;
+    for (int u = cid; u < n_units; u += ncl) {
+      const int split = u / n_st;
       const int kb0 = split * a.kb_per_split, kb1 = min(a.n_kb, kb0 + a.kb_per_split);
       const long long ct0 = clock64();
-      mbar_wait(bar_tempty, uphase ^ 1u);              // epilogue has drained the accumulators
+      if (CTA2) mbar_wait_cluster(bar_tempty, uphase ^ 1u);   // both CTAs' epilogues have drained the accumulators
+      else mbar_wait(bar_tempty, uphase ^ 1u);
       dbg[2] += clock64() - ct0;
       tc_fence_after();
       bool first = true;
@@ -380,6 +474,7 @@ __global__ void __launch_bounds__(384, 1) sparse_mma_kernel(const __grid_constan
         mbar_wait(bar_afull + 8 * as, pa);
         const long long c1 = clock64();
         mbar_wait(bar_xfull + 8 * xs, px);
+        if (CTA2) mbar_wait_cluster(bar_pfull + 8 * as, pa);
         const long long c2 = clock64();
         if (a.debug_clk && lane == 0) { dbg[0] += c1 - c0; dbg[1] += c2 - c1; }
         tc_fence_after();
@@ -389,24 +484,31 @@ __global__ void __launch_bounds__(384, 1) sparse_mma_kernel(const __grid_constan
           for (int h = 0; h < ((a.debug_mode & 2) ? 0 : a.mh); ++h) {
             bool acc = !first;
             for (int p = 0; p < a.n_planes; ++p) {
-              const uint32_t idesc = idesc_bf16((3 - p) * a.l);
+              const uint32_t idesc = CTA2 ? idesc_bf16_m256((3 - p) * a.l) : idesc_bf16((3 - p) * a.l);
               const uint32_t abase = abase0 + p * a.a_plane_bytes + h * 16384;
+              const uint32_t xb = CTA2 ? xbase + (p == 0 ? 0u : p == 1 ? xoff1 : xoff2) : xbase;
 #pragma unroll
               for (int k = 0; k < 4; ++k) {
-                umma_bf16(tmem_base + h * nacc, sw128_desc(abase + k * 32), sw128_desc(xbase + k * 32), idesc, acc ? 1u : 0u);
+                if (CTA2) umma_bf16_2cta(tmem_base + h * nacc, sw128_desc(abase + k * 32), sw128_desc(xb + k * 32), idesc, acc ? 1u : 0u);
+                else umma_bf16(tmem_base + h * nacc, sw128_desc(abase + k * 32), sw128_desc(xb + k * 32), idesc, acc ? 1u : 0u);
                 acc = true;
               }
             }
           }
-          umma_commit(bar_aempty + 8 * as);            // the converters may restore / refill this A stage
-          umma_commit(bar_xempty + 8 * xs);            // the operand slot is free
+          if (CTA2) {
+            umma_commit_2cta(bar_aempty + 8 * as);     // both CTAs' converters may restore / refill this A stage
+            umma_commit_2cta(bar_xempty + 8 * xs);
+          } else {
+            umma_commit(bar_aempty + 8 * as);          // the converters may restore / refill this A stage
+            umma_commit(bar_xempty + 8 * xs);          // the operand slot is free
+          }
         }
         __syncwarp();
         first = false;
         if (++as == a.a_stages) { as = 0; pa ^= 1u; }
         if (++xs == a.x_stages) { xs = 0; px ^= 1u; }
       }
-      if (lane == 0) umma_commit(bar_tfull);
+      if (lane == 0) { if (CTA2) umma_commit_2cta(bar_tfull); else umma_commit(bar_tfull); }
       __syncwarp();
       uphase ^= 1u;
     }
@@ -414,15 +516,17 @@ __global__ void __launch_bounds__(384, 1) sparse_mma_kernel(const __grid_constan
   } else if (warp == 2) {
     // ===== producer of the entry lists =====
     int ls = 0; uint32_t pl = 0;
-    for (int u = blockIdx.x; u < n_units; u += gridDim.x) {
-      const int split = u / a.n_tiles, tile = u - split * a.n_tiles;
+    for (int u = cid; u < n_units; u += ncl) {
+      const int split = u / n_st, st = u - split * n_st;
+      const int tile = CTA2 ? 2 * st + (int)cr : st;
+      const bool tile_ok = tile < a.n_tiles;            // CTA2: an odd number of row tiles leaves the last pair's second CTA empty
       const int kb0 = split * a.kb_per_split, kb1 = min(a.n_kb, kb0 + a.kb_per_split);
-      const uint32_t* tp = a.tile_ptr + (size_t)tile * a.n_kb;
+      const uint32_t* tp = a.tile_ptr + (size_t)(tile_ok ? tile : 0) * a.n_kb;
       uint32_t nv0 = 0, nv1 = 0;
-      if (kb0 + lane < kb1) { nv0 = __ldg(tp + kb0 + lane); nv1 = __ldg(tp + kb0 + lane + 1); }
+      if (tile_ok && kb0 + lane < kb1) { nv0 = __ldg(tp + kb0 + lane); nv1 = __ldg(tp + kb0 + lane + 1); }
       for (int kbg = kb0; kbg < kb1; kbg += 32) {
         const uint32_t v0 = nv0, v1 = nv1;
-        if (kbg + 32 + lane < kb1) { nv0 = __ldg(tp + kbg + 32 + lane); nv1 = __ldg(tp + kbg + 32 + lane + 1); }
+        if (tile_ok && kbg + 32 + lane < kb1) { nv0 = __ldg(tp + kbg + 32 + lane); nv1 = __ldg(tp + kbg + 32 + lane + 1); }
         const int cnt_g = min(32, kb1 - kbg);
         for (int i = 0; i < cnt_g; ++i) {
           uint32_t p0 = __shfl_sync(0xffffffffu, v0, i);
@@ -451,14 +555,15 @@ __global__ void __launch_bounds__(384, 1) sparse_mma_kernel(const __grid_constan
     // ===== epilogue: TMEM -> registers -> global partials =====
     const int q = warp & 3;
     uint32_t uphase = 0;
-    for (int u = blockIdx.x; u < n_units; u += gridDim.x) {
-      const int split = u / a.n_tiles, tile = u - split * a.n_tiles;
+    for (int u = cid; u < n_units; u += ncl) {
+      const int split = u / n_st, st = u - split * n_st;
+      const int tile = CTA2 ? 2 * st + (int)cr : st;
       mbar_wait(bar_tfull, uphase);
       tc_fence_after();
       for (int h = 0; h < a.mh; ++h) {
         const int64_t row = (int64_t)tile * 128 * a.mh + h * 128 + q * 32 + lane;
         float* dst = a.out + (size_t)split * a.split_stride + (size_t)row * a.out_ld;
-        const bool row_ok = row < a.rows_valid;
+        const bool row_ok = row < a.rows_valid && tile < a.n_tiles;
         const bool vec_ok = row_ok && (a.out_ld % 4 == 0) && (a.l <= a.cols_valid);
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + h * nacc;
         for (int c0 = 0; c0 < a.l; c0 += 16) {
@@ -487,7 +592,7 @@ __global__ void __launch_bounds__(384, 1) sparse_mma_kernel(const __grid_constan
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(bar_tempty);
+      if (lane == 0) { if (CTA2 && cr == 1) mbar_arrive_remote(bar_tempty, 0); else mbar_arrive(bar_tempty); }
       uphase ^= 1u;
     }
   } else if (warp >= 8) {
@@ -496,8 +601,8 @@ __global__ void __launch_bounds__(384, 1) sparse_mma_kernel(const __grid_constan
     int as = 0, ls = 0; uint32_t pa = 0, pl = 0;
     uint32_t prev0 = 0, prev1 = 0, prev2 = 0, prev3 = 0;   // entries scattered into each A stage by its previous use
     unsigned long long dbg[6] = {0, 0, 0, 0, 0, 0};
-    for (int u = blockIdx.x; u < n_units; u += gridDim.x) {
-      const int split = u / a.n_tiles;
+    for (int u = cid; u < n_units; u += ncl) {
+      const int split = u / n_st;
       const int kb0 = split * a.kb_per_split, kb1 = min(a.n_kb, kb0 + a.kb_per_split);
       for (int kb = kb0; kb < kb1; ++kb) {
         const uint32_t abase = smem0 + as * a.a_stage_bytes;
@@ -571,14 +676,17 @@ __global__ void __launch_bounds__(384, 1) sparse_mma_kernel(const __grid_constan
   }
   tc_fence_before();
   __syncthreads();
+  if (CTA2) cluster_sync_all();                            // nothing is signalled into a CTA that has left
   if (warp == 1) {
     tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(a.tmem_cols));
+    if (CTA2) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(a.tmem_cols));
+    else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(a.tmem_cols));
   }
 }
 
 // ---- host ---------------------------------------------------------------------------------------
 static int g_sparse_debug_mode = 0;
+static int g_sparse_cta2 = 0;            // 1 = pair kernel (cta_group::2); switched by n2v2r__debug_sparse_cta2 until it is the default
 static unsigned long long* g_sparse_debug_clk = nullptr;
 // K split that balances (row tiles x splits) units over the persistent CTAs
 static int pick_splits(int n_tiles, int n_kb, int max_splits, int grid) {
@@ -609,23 +717,27 @@ int stream_apply_tiles(cudaStream_t s, const StreamPlan& plan, const uint32_t* t
   a.n_kb = (int)(plan.n_pad / 64);
   a.n_tiles = (int)((plan.n + tile_rows - 1) / tile_rows);
   const int grid_max = sm_count();
-  if (plan.k_chunk_user > 0) {                     // the caller fixed the K split (A/B runs against the dense kernel)
-    a.kb_per_split = plan.k_chunk / 64;
-  } else {
-    const int sp = pick_splits(a.n_tiles, a.n_kb, plan.n_splits, grid_max);
-    a.kb_per_split = (a.n_kb + sp - 1) / sp;
-  }
-  a.n_splits = (a.n_kb + a.kb_per_split - 1) / a.kb_per_split;
-  N2V2R_REQUIRE(a.n_splits <= plan.n_splits, "compressed tiles: K split exceeds the workspace plan");
+  const bool cta2 = g_sparse_cta2 != 0 && grid_max >= 2;
   a.a_plane_bytes = 16384u * a.mh;
   a.a_stage_bytes = a.a_plane_bytes * n_planes;
-  a.x_bytes = 3u * plan.l * 128u;
+  // operand stage: the whole split operand [3][l][64], or (pair kernel) this CTA's halves of the first 3l / 2l / l rows
+  a.x_bytes = cta2 ? 128u * (uint32_t)(3 * plan.l / 2 + (n_planes > 1 ? plan.l : 0) + (n_planes > 2 ? plan.l / 2 : 0)) : 3u * plan.l * 128u;
   {
     int tc = 32;
     while (tc < a.mh * 3 * plan.l) tc <<= 1;
     N2V2R_REQUIRE(tc <= 512, "compressed tiles: accumulators do not fit in TMEM");
     a.tmem_cols = (uint32_t)tc;
   }
+  const int units_grid = cta2 ? grid_max / 2 : grid_max;
+  const int n_st = cta2 ? (a.n_tiles + 1) / 2 : a.n_tiles;
+  if (plan.k_chunk_user > 0) {                     // the caller fixed the K split (A/B runs against the dense kernel)
+    a.kb_per_split = plan.k_chunk / 64;
+  } else {
+    const int sp = pick_splits(n_st, a.n_kb, plan.n_splits, units_grid);
+    a.kb_per_split = (a.n_kb + sp - 1) / sp;
+  }
+  a.n_splits = (a.n_kb + a.kb_per_split - 1) / a.kb_per_split;
+  N2V2R_REQUIRE(a.n_splits <= plan.n_splits, "compressed tiles: K split exceeds the workspace plan");
   // shared-memory plan: two A stages, eight landing slots (fewer when tight) and their undo lists first; what is left goes
   // to operand stages (up to 4), then to further A stages (up to 4)
   const uint32_t budget = 227u * 1024u - 512u - 1024u;
@@ -638,7 +750,7 @@ int stream_apply_tiles(cudaStream_t s, const StreamPlan& plan, const uint32_t* t
                 plan.l, n_planes, tile_rows);
   while (a.x_stages < 4 && need(a.a_stages, a.x_stages + 1, a.l_slots) <= budget) ++a.x_stages;
   while (a.a_stages < 4 && need(a.a_stages + 1, a.x_stages, a.l_slots) <= budget) ++a.a_stages;
-  a.off_x = a.a_stages * a.a_stage_bytes;                       // multiples of 1024 (x_bytes = 384 l, l % 16 == 0 -> % 1024 == 0)
+  a.off_x = a.a_stages * a.a_stage_bytes;                       // multiples of 1024 (operand rows come in multiples of 8)
   a.off_land = a.off_x + a.x_stages * a.x_bytes;
   a.off_undo = a.off_land + a.l_slots * (uint32_t)(kLandCap * 8);
   const size_t smem = (size_t)a.off_undo + (size_t)a.a_stages * (kUndoCap * 2) + 1024;
@@ -652,25 +764,50 @@ int stream_apply_tiles(cudaStream_t s, const StreamPlan& plan, const uint32_t* t
   a.tile_ptr = tile_ptr;
   a.entries = (const uint2*)entries;
   a.out = parts;
-  CUtensorMap mX;
-  {
+  CUtensorMap mX, mX1, mX2;
+  if (cta2) {       // the split operand as one [3l x n_pad] matrix; boxes = the halves of its first 3l / 2l / l rows
+    const uint64_t dims[2] = {(uint64_t)plan.n_pad, (uint64_t)(3 * plan.l)};
+    const uint64_t str[1] = {(uint64_t)plan.n_pad * 2};
+    const uint32_t b0[2] = {64, (uint32_t)(3 * plan.l / 2)}, b1[2] = {64, (uint32_t)plan.l}, b2[2] = {64, (uint32_t)(plan.l / 2)};
+    rc = make_map(&mX, xs, 2, dims, str, b0);
+    if (rc == N2V2R_OK) rc = make_map(&mX1, xs, 2, dims, str, b1);
+    if (rc == N2V2R_OK) rc = make_map(&mX2, xs, 2, dims, str, b2);
+    if (rc) return rc;
+  } else {
     const uint64_t dims[3] = {(uint64_t)plan.n_pad, (uint64_t)plan.l, 3};
     const uint64_t str[2] = {(uint64_t)plan.n_pad * 2, (uint64_t)plan.l * plan.n_pad * 2};
     const uint32_t box[3] = {64, (uint32_t)plan.l, 3};
     rc = make_map(&mX, xs, 3, dims, str, box);
     if (rc) return rc;
+    mX1 = mX; mX2 = mX;
   }
   static bool attr_set = false;
   if (!attr_set) {
-    N2V2R_CUDA(cudaFuncSetAttribute(sparse_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024 - 512)));
+    N2V2R_CUDA(cudaFuncSetAttribute(sparse_mma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024 - 512)));
+    N2V2R_CUDA(cudaFuncSetAttribute(sparse_mma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024 - 512)));
     attr_set = true;
   }
-  const int n_units = a.n_tiles * a.n_splits;
-  const int grid = n_units < grid_max ? n_units : grid_max;
+  const int n_units = n_st * a.n_splits;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   rc = mma_events_begin(s, &e0, &e1);
   if (rc) return rc;
-  sparse_mma_kernel<<<grid, 384, smem, s>>>(mX, a);
+  if (cta2) {
+    const int pairs = n_units < units_grid ? n_units : units_grid;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(2 * pairs));
+    cfg.blockDim = dim3(384);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    N2V2R_CUDA(cudaLaunchKernelEx(&cfg, sparse_mma_kernel<true>, mX, mX1, mX2, a));
+  } else {
+    const int grid = n_units < grid_max ? n_units : grid_max;
+    sparse_mma_kernel<false><<<grid, 384, smem, s>>>(mX, mX1, mX2, a);
+  }
   N2V2R_CHECK_LAUNCH();
   rc = mma_events_end(s, e0, e1);
   if (rc) return rc;
@@ -684,6 +821,7 @@ using namespace n2v2r;
 // profiling hook (not part of the ABI header): skip parts of the sparse product kernel to time the rest
 extern "C" void n2v2r__debug_sparse_mode(int mode) { g_sparse_debug_mode = mode; }
 extern "C" void n2v2r__debug_sparse_clk(void* d_buf) { g_sparse_debug_clk = (unsigned long long*)d_buf; }
+extern "C" void n2v2r__debug_sparse_cta2(int on) { g_sparse_cta2 = on; }
 
 // ---- C ABI: building the compressed tiles --------------------------------------------------------
 extern "C" int n2v2r_tiles_count(void* stream, const float* d_in, int64_t n, int64_t ld, uint32_t* d_counts, uint32_t* d_counts_t,

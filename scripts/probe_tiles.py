@@ -40,6 +40,16 @@ def timed(layer, k_chunk=0):
 
 ms_t, y_t = timed(Lt)
 out["tiles_ms"] = ms_t
+if "--cta2" in sys.argv:                        # the CTA-pair kernel (cta_group::2) against the one-CTA kernel
+    import ctypes
+    N.load().n2v2r__debug_sparse_cta2(ctypes.c_int(1))
+    try:
+        ms_2, y_2 = timed(Lt)
+        out["tiles_cta2_ms"] = ms_2
+        out["cta2_bit_identical"] = bool(torch.equal(y_2.view(torch.int32), y_t.view(torch.int32)))
+        out["cta2_max_abs_diff"] = float((y_2 - y_t).abs().max())
+    finally:
+        N.load().n2v2r__debug_sparse_cta2(ctypes.c_int(0))
 if "--debug-modes" in sys.argv:                 # profiling: the kernel without its converters / without its MMAs (wrong results)
     import ctypes
     names = ["mma:wait_a_full", "mma:wait_x_full", "mma:wait_tmem_empty", "-", "conv:wait_a_empty", "conv:restore", "conv:bar", "conv:wait_landing",
