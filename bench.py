@@ -72,7 +72,7 @@ def parse_args():
                          "expanded in shared memory for sparse layers; auto = the product default")
     ap.add_argument("--no-cross-check", action="store_true",
                     help="skip the untimed second solve (other seed, l = 80) whose subspace angle against the timed solve is reported")
-    ap.add_argument("--seed-batch", type=int, default=3,
+    ap.add_argument("--seed-batch", type=int, default=6,
                     help="workload c5: solves that run concurrently and share every pass over a layer (1 = one after the other)")
     ap.add_argument("--cpu-ladder", default="2000,4000,8000",
                     help="--impl reference: node counts the reference path is timed at (all layers), ascending")
@@ -246,22 +246,37 @@ def cpu_cores_used():
     return max(1, n - 1)        # joblib n_jobs=-2 in Borda; ARPACK / csc matvec / scipy distances are single-threaded
 
 
-# How each phase of the reference path grows with the node count n (T, dims, metrics fixed): the fit is ARPACK on CSC layers
-# (passes over T n^2 rho non-zeros, more restarts as n grows: measured exponent 2.2-2.5), the distances are n Python calls
-# per column (linear), the faithful Borda is list.index per node per column (quadratic).  Used only where a size was NOT
-# measured; exponents fitted on the ladder replace the defaults when at least two sizes were measured.
-PHASE_EXPONENT = {"fit": 2.0, "distances": 1.0, "borda": 2.0}
+# How each phase of the reference path grows with the node count n (T, dims, metrics fixed), used to extrapolate the largest
+# MEASURED size to the full one.  Measured on the ladder n = 2000 / 4000 / 8000 (8 cores, profiles/README.md): the fit (ARPACK
+# on CSC layers) grows only ~n^0.9 there although a pass over the layers costs n^2 -- the planted spectrum separates from the
+# noise bulk as n grows and ARPACK needs fewer restarts; the distances are n Python calls per column (linear; small sizes are
+# overhead-bound, measured 0.6-0.7); the faithful Borda is list.index per node per column in joblib workers (quadratic;
+# measured 1.8 between the two largest rungs, less below where process start-up dominates).  The extrapolation takes the
+# LOCAL slope of the two largest measured sizes, clamped to [floor, cap]: never below linear (every phase touches every node
+# at least once per column / per pass), never above the phase's asymptotic law.  PHASE_EXPONENT is used when only one size
+# was measured (the in-run cpu_baseline of the B200 arm).
+PHASE_EXPONENT = {"fit": 1.0, "distances": 1.0, "borda": 1.8}
+PHASE_FLOOR = {"fit": 1.0, "distances": 1.0, "borda": 1.0}
+PHASE_CAP = {"fit": 2.4, "distances": 1.0, "borda": 2.0}
 
 
 def fit_exponents(points):
-    """Least-squares slope of log(seconds) against log(n) per phase over the measured ladder."""
+    """Per phase: slope of log(seconds) against log(n) between the two largest measured sizes, clamped to [floor, cap]."""
     out = dict(PHASE_EXPONENT)
     if len(points) >= 2:
-        ln = np.log([p["n"] for p in points])
+        a, b = points[-2], points[-1]
         for ph in PHASE_EXPONENT:
-            t = np.asarray([max(p[ph], 1e-6) for p in points])
-            out[ph] = float(np.polyfit(ln, np.log(t), 1)[0])
+            slope = float(np.log(max(b[ph], 1e-6) / max(a[ph], 1e-6)) / np.log(b["n"] / a["n"]))
+            out[ph] = float(min(PHASE_CAP[ph], max(PHASE_FLOOR[ph], slope)))
     return out
+
+
+def raw_slopes(points):
+    """The unclamped slopes (reported next to the clamped exponents)."""
+    if len(points) < 2:
+        return {}
+    a, b = points[-2], points[-1]
+    return {ph: float(np.log(max(b[ph], 1e-6) / max(a[ph], 1e-6)) / np.log(b["n"] / a["n"])) for ph in PHASE_EXPONENT}
 
 
 def extrapolate(point, n_full, exps):
@@ -317,11 +332,12 @@ def run_reference_arm(args):
         sample = (f"MEASURED: the reference path once per size, all {w['T']} layers, sizes n = {[p['n'] for p in points]}: totals "
                   f"{[round(p['total'], 2) for p in points]} s (largest: fit {top['fit']:.2f}, distances {top['distances']:.2f}, borda "
                   f"{top['borda']:.2f}).  EXTRAPOLATED to n = {w['n']}: each phase of the largest measured size scaled by "
-                  f"(n_full/n)^e with the exponents fitted on the ladder (fit {exps['fit']:.2f}, distances {exps['distances']:.2f}, "
-                  f"borda {exps['borda']:.2f}) -> fit {parts['fit']:.0f} s, distances {parts['distances']:.0f} s, borda {parts['borda']:.0f} s"
+                  f"(n_full/n)^e, e = the slope between the two largest measured sizes clamped to [1, the phase's asymptotic law] "
+                  f"(fit {exps['fit']:.2f}, distances {exps['distances']:.2f}, borda {exps['borda']:.2f}) -> fit {parts['fit']:.0f} s, distances {parts['distances']:.0f} s, borda {parts['borda']:.0f} s"
                   + (f", x {runs} runs" if runs > 1 else "") + ".  value is that extrapolation, not a measurement at full size "
                   f"(the full size needs > 150 GB of host RAM and hours).")
         extra = {"measured": points, "measured_n": top["n"], "measured_s": top["total"], "exponents": exps,
+                 "measured_slopes_last_two": raw_slopes(points),
                  "extrapolated_s": full, "extrapolated_phases_s": parts,
                  "cores_by_phase": {"fit": 1, "distances": 1, "borda": cores},
                  "ladder_wall_s": time.perf_counter() - t_begin}
@@ -448,8 +464,8 @@ def cpu_baseline_leg(w, n, T):
     return {"value": one_run * runs, "unit": "s", "cores": cpu_cores_used(), "kind": "port",
             "cores_by_phase": {"fit": 1, "distances": 1, "borda": cpu_cores_used()},
             "sample": f"MEASURED at n={n_s} of {n} nodes, all {T} layers, one run of {runs}: {pt['total']:.2f} s (fit {pt['fit']:.2f}, distances "
-                      f"{pt['distances']:.2f}, borda {pt['borda']:.2f}).  EXTRAPOLATED per phase: fit x (n/n_s)^{PHASE_EXPONENT['fit']:g} "
-                      f"(optimistic for the reference: its measured growth is n^2.2-2.5, see `bench.py --impl reference`), distances x "
+                      f"{pt['distances']:.2f}, borda {pt['borda']:.2f}).  EXTRAPOLATED per phase with the exponents the reference arm's ladder "
+                      f"gives (`bench.py --impl reference`, n up to 8000): fit x (n/n_s)^{PHASE_EXPONENT['fit']:g}, distances x "
                       f"(n/n_s)^{PHASE_EXPONENT['distances']:g}, borda x (n/n_s)^{PHASE_EXPONENT['borda']:g} -> fit {parts['fit']:.0f} s, "
                       f"distances {parts['distances']:.0f} s, borda {parts['borda']:.0f} s" + (f", x {runs} runs" if runs > 1 else ""),
             "sample_seconds": pt["total"], "measured_n": n_s, "measured_s": pt["total"],
@@ -478,7 +494,8 @@ def build_workload_layers(w, n, layer_ids, want_f32=False, storage="auto", graph
     return layers, f32s, events
 
 
-def hot_path(layers, w, l, seed=SOLVER_SEED, T_global=None, layer_offset=0, gather=None, dims=None, metrics=None, shard=None):
+def hot_path(layers, w, l, seed=SOLVER_SEED, T_global=None, layer_offset=0, gather=None, dims=None, metrics=None, shard=None,
+             slab_group=None):
     """One step of the benchmark: UASE solve at k = max(dims) with the gap-aware stop at every swept d, distances for every
     (d, metric), rank + Borda of all comparisons.  Returns (info, emb (T, n, k), scores (C, cols, n), bordas (C, n)).
     shard = (rank, world, all_reduce): the (d, metric) columns of the sweep are split over the ranks (every rank holds all
@@ -490,7 +507,7 @@ def hot_path(layers, w, l, seed=SOLVER_SEED, T_global=None, layer_offset=0, gath
     dims = DIMS if dims is None else dims
     names, cdims, cmets = D.column_specs(dims, METRICS if metrics is None else metrics)
     emb, sigma, _, info = D.uase(layers, max(dims), l=l, tol=1e-5, max_iters=400, seed=seed, check_dims=dims,
-                                 T_global=T_global or len(layers), layer_offset=layer_offset)
+                                 T_global=T_global or len(layers), layer_offset=layer_offset, slab_group=slab_group)
     info["sigma"] = sigma
     if gather is not None:
         emb = gather(emb)
@@ -507,14 +524,14 @@ def hot_path(layers, w, l, seed=SOLVER_SEED, T_global=None, layer_offset=0, gath
     return info, emb, scores, bordas
 
 
-def cross_solve_check(layers, w, l, emb, bordas, T_global, layer_offset, gather, shard=None):
+def cross_solve_check(layers, w, l, emb, bordas, T_global, layer_offset, gather, shard=None, slab_group=None):
     """UNTIMED parity evidence at full size: a second, independent solve (other start block, wider block l = 80) and the
     principal angle between the two embeddings' subspaces at every swept d (device.subspace_sin_angles), plus the agreement
     of the two Borda tables.  Two solves that share nothing but the layers agree to 1e-4 only if both are converged."""
     from node2vec2rank_b200 import device as D
     l2 = 80 if l != 80 else 64
     info2, emb2, _, bordas2 = hot_path(layers, w, l2, seed=SOLVER_SEED + 1000003, T_global=T_global, layer_offset=layer_offset,
-                                       gather=gather, shard=shard)
+                                       gather=gather, shard=shard, slab_group=slab_group)
     ang = D.subspace_sin_angles(emb, emb2, DIMS)
     a, b = bordas.double(), bordas2.double()
     a = a - a.mean(dim=1, keepdim=True)
@@ -543,17 +560,32 @@ def run_b200_arm(args):
     barrier, reduce_max = env.barrier, env.reduce_max
     hbm_peak, peak_src = env.hbm_peak, env.hbm_src
     n, T, K, l = w["n"], w["T"], w["K"], args.block_width
+    slab_group, slab_rows = None, None
     if world > T:
-        raise SystemExit(f"workload {args.workload} has {T} layers: at most {T} ranks (row-slab sharding is not implemented)")
-    mine = ND.layer_partition(T, world, rank)
+        # fewer layers than GPUs: every layer is cut into world / T row slabs; rank r holds slab r % S of layer r // S
+        if world % T:
+            raise SystemExit(f"workload {args.workload} has {T} layers: the number of ranks must be a multiple of {T} (row slabs per layer)")
+        S = world // T
+        mine = range(rank // S, rank // S + 1)
+        slab_rows = ND.layer_partition(n, S, rank % S)
+        for t in range(T):                         # every rank creates every group (torch.distributed rule)
+            g = tdist.new_group(list(range(t * S, (t + 1) * S)))
+            if t == rank // S:
+                slab_group = g
+    else:
+        mine = ND.layer_partition(T, world, rank)
     Bs = block_probabilities(w)
 
     # ---- setup (untimed): K0 generate + K1 load pass per local layer -------------------------------
     t_setup = time.perf_counter()
-    layers, f32s, pre_events = build_workload_layers(w, n, mine, want_f32=not args.no_e2e, storage=args.layer_storage)
+    want_host = not args.no_e2e and slab_rows is None
+    layers, f32s, pre_events = build_workload_layers(w, n, mine, want_f32=want_host or slab_rows is not None,
+                                                     storage="planes" if slab_rows is not None else args.layer_storage)
+    if slab_rows is not None:                      # keep only this rank's rows of its layer (and their transpose)
+        layers = [D.make_slab_layer(f, slab_rows.start, len(slab_rows), n_planes=L.n_planes) for f, L in zip(f32s, layers)]
     host_graphs = []
     for f32 in f32s:
-        if f32 is not None:            # what the reference's DataLoader hands to N2V2R: float32 (n, n) on the HOST (pinned)
+        if f32 is not None and want_host:  # what the reference's DataLoader hands to N2V2R: float32 (n, n) on the HOST (pinned)
             h = torch.empty((n, n), dtype=torch.float32, pin_memory=True)
             h.copy_(f32)
             host_graphs.append(h.numpy())
@@ -563,13 +595,22 @@ def run_b200_arm(args):
     storage = layers[0].storage if layers else "planes"
     setup_s = time.perf_counter() - t_setup
     preprocess_ms = float(np.mean([a.elapsed_time(b) for a, b in pre_events][1:] or [a.elapsed_time(b) for a, b in pre_events]))
-    layers_gb = sum(L.nbytes for L in layers) * T / max(len(layers), 1) / 1e9
+    layers_gb = sum(L.nbytes for L in layers) * (world if slab_rows is not None else T / max(len(layers), 1)) / 1e9
     offset = mine.start if len(mine) else 0
-    gather = (lambda e: ND.gather_layers(e, T)) if world > 1 else None
+    if slab_rows is not None:                      # every rank of a layer group holds the layer's embedding: take one per group
+        S_ = world // T
+
+        def gather(e):
+            out = torch.empty((world,) + tuple(e.shape[1:]), dtype=e.dtype, device=e.device)
+            tdist.all_gather_into_tensor(out, e.contiguous())
+            return out[::S_].contiguous()
+    else:
+        gather = (lambda e: ND.gather_layers(e, T)) if world > 1 else None
     shard = (rank, world, lambda t: tdist.all_reduce(t)) if world > 1 else None
 
     def step():
-        info, emb, scores, bordas = hot_path(layers, w, l, T_global=T, layer_offset=offset, gather=gather, shard=shard)
+        info, emb, scores, bordas = hot_path(layers, w, l, T_global=T, layer_offset=offset, gather=gather, shard=shard,
+                                             slab_group=slab_group)
         launches = info["kernel_launches"] + 2
         return info, scores, bordas, launches, emb
 
@@ -596,7 +637,7 @@ def run_b200_arm(args):
     clocks = sampler.stop() if rank == 0 else None
     sweep_ms = reduce_max(float(np.mean([max(0.0, ms_step - i["total_ms"]) for i in infos])))      # step minus solve
     # ---- untimed parity evidence: independent second solve, subspace angle per swept d ----------------
-    cross = None if args.no_cross_check else cross_solve_check(layers, w, l, emb, bordas, T, offset, gather, shard)
+    cross = None if args.no_cross_check else cross_solve_check(layers, w, l, emb, bordas, T, offset, gather, shard, slab_group)
     del emb
 
     # ---- roofline of the dominant kernel (tcgen05 streaming product), measured live in the timed steps ----
@@ -604,7 +645,7 @@ def run_b200_arm(args):
 
     # ---- e2e: the public API on host buffers ------------------------------------------------------------
     e2e = None
-    if not args.no_e2e:
+    if not args.no_e2e and slab_rows is None:
         del layers, scores, bordas
         torch.cuda.empty_cache()
         cfg = dict(embed_dimensions=DIMS, distance_metrics=METRICS, comp_strategy=w["strategy"], seed=SOLVER_SEED,
@@ -661,6 +702,7 @@ def run_b200_arm(args):
         "data": "synthetic",
         "config": {"workload": w["name"], "n": n, "layers": T, "communities": K, "block_width": l, "planes_per_layer": n_planes,
                    "layers_per_gpu": len(mine), "layer_storage": storage,
+                   "row_slabs_per_layer": (world // T if slab_rows is not None else 1),
                    "l2_policy": f"inputs larger than L2: the {T} layers ({layers_gb:.1f} GB in "
                                 f"total, every pass streams one of them) against 0.126 GB of L2; no flush needed",
                    "operator_applications": last["iterations"], "layer_passes": last["layer_passes"],
@@ -726,7 +768,8 @@ def stream_roofline(env, infos, ms_step, steps, n, n_planes, l, workload, layers
     else:
         e4m3 = bool(layers) and layers[0].storage == "e4m3"
         per_entry = 1.0 if e4m3 else 2.0 * n_planes
-        alg_bytes = float(n) * n * per_entry + 4.0 * l * 2.0 * n               # matrix once + skinny in + skinny out
+        rows = layers[0].rows if (layers and layers[0].rows) else n              # a row slab streams rows x n entries per pass
+        alg_bytes = float(rows) * n * per_entry + 4.0 * l * (n + rows)         # matrix once + skinny in + skinny out
         achieved = alg_bytes / avg_s / 1e9 if mma_n else 0.0
         roof = {"bound": "hbm", "achieved": achieved, "peak": env.hbm_peak, "unit": "GB/s", "frac": achieved / env.hbm_peak,
                 "traffic": None, "kernel": "stream_mma8_kernel" if e4m3 else "stream_mma_kernel", "peak_source": env.hbm_src,

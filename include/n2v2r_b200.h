@@ -182,6 +182,10 @@ typedef struct {
   int64_t n_entries, n_entries_t;
   int32_t tile_rows;             /* 128 or 256                                           */
   int32_t reserved;
+  /* ROW SLAB of a layer (bf16 planes only; sharding of ONE layer over several processes when there are fewer layers
+   * than GPUs): rows > 0 means this process holds rows [row_offset, row_offset + rows) of the n x n layer:
+   * d_planes = the slab (rows x ld), d_planes_t = its transpose (n x ld_t, ld_t a multiple of 64 >= rows; required). */
+  int64_t row_offset, rows, ld_t;
 } n2v2r_layer_t;
 
 typedef struct {
@@ -207,6 +211,8 @@ typedef struct {
   int32_t trace;           /* 1 = one line per outer iteration on stderr                 */
   int32_t comm_mode;       /* how Y is summed over the processes: 0 = `allreduce` callback, 1 = `user` is an
                               ncclComm_t and the library calls ncclAllReduce itself on `stream` */
+  void* group_comm;        /* row slabs: communicator (n2v2r_comm_init) of the processes that hold slabs of the SAME layers
+                              as this one; Z_t = sum over the slabs of slab^T Q[slab rows] is all-reduced over it        */
   void* batch;             /* seed batching: handle of n2v2r_batch_create shared by concurrent solves, or NULL */
   int32_t batch_slot;      /* this solve's slot in the batch, 0 .. participants-1                              */
   int32_t reserved2;

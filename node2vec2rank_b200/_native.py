@@ -35,7 +35,8 @@ class Layer(C.Structure):
     _fields_ = [("d_planes", C.c_void_p), ("d_planes_t", C.c_void_p), ("n_planes", C.c_int32),
                 ("storage", C.c_int32), ("ld", C.c_int64),
                 ("d_tile_ptr", C.c_void_p), ("d_entries", C.c_void_p), ("d_tile_ptr_t", C.c_void_p), ("d_entries_t", C.c_void_p),
-                ("n_entries", C.c_int64), ("n_entries_t", C.c_int64), ("tile_rows", C.c_int32), ("reserved", C.c_int32)]
+                ("n_entries", C.c_int64), ("n_entries_t", C.c_int64), ("tile_rows", C.c_int32), ("reserved", C.c_int32),
+                ("row_offset", C.c_int64), ("rows", C.c_int64), ("ld_t", C.c_int64)]
 
 
 class UaseParams(C.Structure):
@@ -44,7 +45,7 @@ class UaseParams(C.Structure):
                 ("cheb_degree", C.c_int32), ("algo", C.c_int32), ("k_chunk", C.c_int32), ("n_check", C.c_int32),
                 ("tol", C.c_double), ("seed", C.c_uint64), ("h_check_dims", C.POINTER(C.c_int32)),
                 ("floor_mult", C.c_double), ("rel_floor", C.c_double), ("first_degree", C.c_int32), ("no_early_lock", C.c_int32),
-                ("trace", C.c_int32), ("comm_mode", C.c_int32), ("batch", C.c_void_p), ("batch_slot", C.c_int32),
+                ("trace", C.c_int32), ("comm_mode", C.c_int32), ("group_comm", C.c_void_p), ("batch", C.c_void_p), ("batch_slot", C.c_int32),
                 ("reserved2", C.c_int32)]
 
 

@@ -13,6 +13,8 @@ namespace n2v2r {
 
 int stream_apply_tcgen05(cudaStream_t s, const StreamPlan& plan, const void* planes, int n_planes, int64_t ld,
                          const float* x, __nv_bfloat16* xs, float* parts, float* out, int accumulate);  // k3_tcgen05.cu
+int stream_apply_rect(cudaStream_t s, const StreamPlan& plan, const void* planes, int n_planes, int64_t ld, int64_t rows_out,
+                      int64_t k_len, const float* x, __nv_bfloat16* xs, float* parts, float* out, int accumulate);   // k3_tcgen05.cu
 int stream_apply_e4m3(cudaStream_t s, const StreamPlan& plan, const void* plane8, int64_t ld8, const float* x, void* xs_ws,
                       float* parts, float* out, int accumulate);                                        // k3_fp8.cu
 int stream_apply_tiles(cudaStream_t s, const StreamPlan& plan, const uint32_t* tile_ptr, const void* entries, int n_planes,
@@ -100,8 +102,19 @@ int make_stream_plan(int64_t n, int l, int algo, int k_chunk, StreamPlan* plan) 
   return N2V2R_OK;
 }
 
+int stream_apply_slab(cudaStream_t s, const StreamPlan& plan, const n2v2r_layer_t& L, int transpose, const float* x,
+                      __nv_bfloat16* xs, float* parts, float* out, int accumulate, double* bytes_moved) {
+  N2V2R_REQUIRE(L.storage == N2V2R_STORE_PLANES && plan.algo == N2V2R_ALGO_TCGEN05, "row slabs: bf16 planes on the tcgen05 path only");
+  N2V2R_REQUIRE(L.rows > 0 && L.row_offset >= 0 && L.row_offset + L.rows <= plan.n && L.d_planes && L.d_planes_t && L.ld_t >= L.rows,
+                "row slab: need rows inside the layer, the slab and its transpose");
+  if (bytes_moved) *bytes_moved += (double)L.rows * (double)plan.n * 2.0 * L.n_planes + 4.0 * plan.l * (double)(plan.n + L.rows);
+  if (transpose) return stream_apply_rect(s, plan, L.d_planes_t, L.n_planes, L.ld_t, plan.n, L.rows, x, xs, parts, out, accumulate);
+  return stream_apply_rect(s, plan, L.d_planes, L.n_planes, L.ld, L.rows, plan.n, x, xs, parts, out, accumulate);
+}
+
 int stream_apply(cudaStream_t s, const StreamPlan& plan, const n2v2r_layer_t& L, int transpose, const float* x,
                  __nv_bfloat16* xs, float* parts, float* out, int accumulate, double* bytes_moved) {
+  N2V2R_REQUIRE(L.rows == 0, "row-slab layers go through stream_apply_slab");
   if (L.storage == N2V2R_STORE_TILES) {
     const uint32_t* tp = (transpose && L.d_tile_ptr_t) ? L.d_tile_ptr_t : L.d_tile_ptr;
     const void* en = (transpose && L.d_entries_t) ? L.d_entries_t : L.d_entries;

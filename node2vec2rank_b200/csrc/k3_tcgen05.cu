@@ -423,6 +423,23 @@ int stream_apply_tcgen05(cudaStream_t s, const StreamPlan& plan, const void* pla
   return launch_reduce_parts(s, parts, plan.n_splits, rows_pad, plan.n, plan.l, out, accumulate);
 }
 
+// Rectangular product for row slabs: out (rows_out x l) (= or +=) S x, S = n_planes planes of rows_out x k_len (leading dimension
+// ld), x (k_len x l).  Same kernel, same K split; the workspace of the square plan (n >= rows_out, k_len) is large enough.
+int stream_apply_rect(cudaStream_t s, const StreamPlan& plan, const void* planes, int n_planes, int64_t ld, int64_t rows_out,
+                      int64_t k_len, const float* x, __nv_bfloat16* xs, float* parts, float* out, int accumulate) {
+  N2V2R_REQUIRE(xs && parts && planes, "slab product needs its workspace");
+  N2V2R_REQUIRE(rows_out > 0 && k_len > 0 && rows_out <= plan.n && k_len <= plan.n && ld >= k_len && ld % 64 == 0, "slab product: bad shape");
+  const int64_t k_pad = round_up(k_len, 64);
+  int rc = launch_split_transpose(s, x, k_len, plan.l, k_pad, xs);
+  if (rc) return rc;
+  const int64_t rows_pad = round_up(rows_out, 256);
+  const int n_splits = (int)((k_pad + plan.k_chunk - 1) / plan.k_chunk);
+  rc = launch_mma(s, planes, n_planes, rows_out, ld, (size_t)rows_out * ld * sizeof(__nv_bfloat16), xs, plan.l, k_pad, plan.l, 1, k_pad,
+                  plan.k_chunk, parts, plan.l, rows_pad * plan.l, rows_pad, plan.l);
+  if (rc) return rc;
+  return launch_reduce_parts(s, parts, n_splits, rows_pad, rows_out, plan.l, out, accumulate);
+}
+
 // Seed batching: out_i (= or +=) A x_i for nb operands with ONE read of the layer.  xs: [nb][3][l][n_pad] bf16, parts:
 // [n_splits][rows_pad][nb * l].  Every out_i has exactly the bits of the unbatched product (same K split, same MMA order per
 // row; the 128- instead of 256-row tiles do not change a row's accumulation).

@@ -41,5 +41,9 @@ int make_stream_plan(int64_t n, int l, int algo, int k_chunk, StreamPlan* plan);
 // xs / parts: scratch sized by the plan (may be null for the SIMT algo).
 int stream_apply(cudaStream_t s, const StreamPlan& plan, const n2v2r_layer_t& L, int transpose, const float* x,
                  __nv_bfloat16* xs, float* parts, float* out, int accumulate, double* bytes_moved);
+// row slab of a layer (L.rows > 0): transpose = 0: out[0..rows) (+)= slab x (x: n x l);  transpose = 1: out (n x l) (+)= slab^T x
+// (x: rows x l).  The caller offsets the pointers into the full n x l blocks.
+int stream_apply_slab(cudaStream_t s, const StreamPlan& plan, const n2v2r_layer_t& L, int transpose, const float* x,
+                      __nv_bfloat16* xs, float* parts, float* out, int accumulate, double* bytes_moved);
 
 }  // namespace n2v2r

@@ -132,6 +132,11 @@ extern "C" int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2
       sink_guard(p->algo == N2V2R_ALGO_TCGEN05 ? &mma_evs : nullptr);
   N2V2R_CUDA(cudaEventRecord(ev_all0, s));
   const int per_pass = (p->algo == N2V2R_ALGO_TCGEN05 ? 3 : 1);
+  bool slabs = false;
+  for (int t = 0; t < T; ++t) slabs = slabs || L[t].rows > 0;
+  for (int t = 0; t < T; ++t) N2V2R_REQUIRE(!slabs || L[t].rows > 0, "uase: row-slab and whole layers cannot be mixed");
+  N2V2R_REQUIRE(!slabs || (p->comm_mode == 1 && user), "uase: row slabs need the library-owned NCCL communicator (comm_mode = 1)");
+  N2V2R_REQUIRE(!slabs || !p->batch, "uase: row slabs and seed batching cannot be combined");
 
   // one pass of CholeskyQR: dst = X chol(X^T X)^-1
   auto cholqr_pass = [&](const float* X, float* dst) -> int {
@@ -149,6 +154,17 @@ extern "C" int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2
     N2V2R_CUDA(cudaEventRecord(e0, s));
     if (p->batch) {                          // served together with the other solves of the batch (batch.cu)
       RC(batch_apply(p->batch, p->batch_slot, x, out, keep_z ? b.Z : nullptr, b.Zt, s));
+    } else if (slabs) {
+      // row slabs (fewer layers than GPUs): this rank holds rows [r0, r0 + m) of each of its layers.  Z_t = sum over the
+      // slabs of slab^T x[slab rows] (all-reduce inside the layer's group); out[slab rows] += slab Z_t; the global all-reduce
+      // below adds the layers and assembles the slabs.
+      N2V2R_CUDA(cudaMemsetAsync(out, 0, sizeof(float) * nl, s));
+      for (int t = 0; t < T; ++t) {
+        float* z = keep_z ? b.Z + t * nl : b.Zt;
+        RC(stream_apply_slab(s, plan, L[t], 1, x + (size_t)L[t].row_offset * l, b.xs, b.parts, z, 0, &stats.stream_bytes));
+        if (p->group_comm) RC(comm_allreduce_f32(p->group_comm, z, (int64_t)nl, s));
+        RC(stream_apply_slab(s, plan, L[t], 0, z, b.xs, b.parts, out + (size_t)L[t].row_offset * l, 1, &stats.stream_bytes));
+      }
     } else {
       for (int t = 0; t < T; ++t) {
         float* z = keep_z ? b.Z + t * nl : b.Zt;
@@ -161,7 +177,7 @@ extern "C" int n2v2r_uase(void* stream, const n2v2r_uase_params_t* p, const n2v2
     stats.layer_passes += 2 * T;
     stats.kernel_launches += 2 * T * per_pass;
     stats.iterations += 1;
-    if (p->comm_mode == 1 && user && p->T_local != p->T_global) {
+    if (p->comm_mode == 1 && user && (p->T_local != p->T_global || slabs)) {
       RC(comm_allreduce_f32(user, out, (int64_t)nl, s));
     } else if (allreduce && allreduce(user, out, (int64_t)nl, N2V2R_F32, stream) != 0) {
       set_error("uase: all-reduce callback failed (Y)");

@@ -40,6 +40,9 @@ class DeviceLayer:
     entries_t: torch.Tensor | None = None
     n_entries: int = 0                     # entries in use (the arrays hold at least one allocation unit)
     n_entries_t: int = 0
+    row_offset: int = 0                    # row slab of a layer (make_slab_layer): rows [row_offset, row_offset + rows)
+    rows: int = 0                          # 0 = the whole layer
+    ld_t: int = 0
     dtype = np.float32
 
     def __post_init__(self):
@@ -55,9 +58,10 @@ class DeviceLayer:
                            self.tile_ptr.data_ptr(), self.entries.data_ptr(),
                            0 if self.tile_ptr_t is None else self.tile_ptr_t.data_ptr(),
                            0 if self.entries_t is None else self.entries_t.data_ptr(),
-                           self.n_entries, self.n_entries_t, self.tile_rows, 0)
+                           self.n_entries, self.n_entries_t, self.tile_rows, 0, 0, 0, 0)
         return N.Layer(self.planes.data_ptr(), 0 if self.planes_t is None else self.planes_t.data_ptr(),
-                       self.n_planes, N.STORE_E4M3 if self.storage == "e4m3" else N.STORE_PLANES, self.ld, 0, 0, 0, 0, 0, 0, 0, 0)
+                       self.n_planes, N.STORE_E4M3 if self.storage == "e4m3" else N.STORE_PLANES, self.ld, 0, 0, 0, 0, 0, 0, 0, 0,
+                       self.row_offset, self.rows, self.ld_t)
 
     def to_dense(self):
         """fp32 (n, n) device tensor reconstructed from the stored form (exact)."""
@@ -68,7 +72,7 @@ class DeviceLayer:
             return out
         if self.storage == "e4m3":
             return self.planes[0, :, :self.n].view(torch.float8_e4m3fn).to(torch.float32)
-        return self.planes[:, :, :self.n].to(torch.float32).sum(dim=0)
+        return self.planes[:, :, :self.n].to(torch.float32).sum(dim=0)      # a row slab gives its (rows, n) block
 
     def to_e4m3(self):
         """The same layer as ONE e4m3 plane (1 byte per entry, N2V2R_STORE_E4M3): for one-plane layers whose values e4m3
@@ -317,6 +321,24 @@ def project(W: torch.Tensor, on):
 
 
 E4M3_AUTO = False               # storage="auto": binarised layers as one e4m3 plane (set after measuring, see profiles/)
+def make_slab_layer(x32: torch.Tensor, row_offset: int, rows: int, n_planes=None):
+    """Row slab of a layer for sharding ONE layer over several GPUs (fewer layers than GPUs): x32 is the (n, n)
+    fp32 device matrix (or just its rows [row_offset, row_offset + rows)); the slab and its transpose are stored as bf16
+    planes.  The solver (device.uase with a group communicator) all-reduces Z_t over the ranks that hold the other slabs."""
+    n = x32.shape[1]
+    block = x32 if x32.shape[0] == rows else x32[row_offset:row_offset + rows]
+    if block.shape != (rows, n):
+        raise ValueError("make_slab_layer: rows outside the matrix")
+    block = block.contiguous()
+    P = n_planes or planes_needed(block)
+    _, planes, ld_p, cs = transform(block, n_planes=P, want_colsum=True)                # (P, rows, ld_n)
+    ld_t = (rows + 63) // 64 * 64
+    planes_t = torch.zeros((P, n, ld_t), dtype=torch.bfloat16, device=block.device)
+    planes_t[:, :, :rows] = planes[:, :, :n].transpose(1, 2)                            # build-time plumbing, not on the hot path
+    return DeviceLayer(planes=planes, n=n, ld=ld_p, n_planes=P, symmetric=False, planes_t=planes_t, colsum=cs,
+                       row_offset=int(row_offset), rows=int(rows), ld_t=ld_t)
+
+
 TILES_MAX_DENSITY = 0.08        # layers sparser than this are stored as compressed tiles (storage="auto")
 TILES_MIN_N = 4096              # ... when they are large enough for the streaming product to matter
 
@@ -386,6 +408,7 @@ def make_layer(x32: torch.Tensor, n_planes=None, colsum=None, check_symmetry=Tru
 PACK_MIN_ENTRIES = 4_000_000          # below this a layer crosses PCIe dense (the packed pipeline has fixed costs)
 PACK_CHUNK_ENTRIES = 300_000_000      # rows are packed and copied in chunks of about this many entries
 PACK_MAX_DENSITY = 0.3                # staging capacity for the non-zero values, as a fraction of a chunk's entries
+PACK_SLOTS = 3                        # pinned staging slots: packed chunks in flight behind a dense chunk on the copy engine
 PACK_DENSE_EVERY = 4                  # pinned sources: every 4th row chunk crosses PCIe dense on its own stream while the host
                                       # cores pack the others (packing runs at ~150 GB/s of host reads, the otherwise idle copy
                                       # engine adds ~55 GB/s); 0 = pack every chunk
@@ -413,7 +436,7 @@ def _staging(chunk_rows, cols):
         _pack_staging.clear()                                      # one shape at a time stays pinned
         _pack_staging[key] = [dict(bitmap=torch.empty((chunk_rows, words), dtype=torch.int32, pin_memory=True),
                                    values=torch.empty(cap, dtype=torch.float32, pin_memory=True),
-                                   row_start=torch.empty(chunk_rows, dtype=torch.int64, pin_memory=True)) for _ in range(2)]
+                                   row_start=torch.empty(chunk_rows, dtype=torch.int64, pin_memory=True)) for _ in range(PACK_SLOTS)]
     return _pack_staging[key]
 
 
@@ -484,24 +507,22 @@ def _layers_from_host_packed(srcs, n_planes, chunk_rows, slots, storage="auto"):
                         copy.wait_event(done)
                         copy2.wait_event(done)
                     out = dense[t % 2]
-                    if hybrid and not dense_mode:         # queue this layer's dense chunks first: the copy engine starts at once
-                        with torch.cuda.stream(copy2):
-                            for ci, r0 in enumerate(range(0, rows, chunk_rows)):
-                                if ci % PACK_DENSE_EVERY == PACK_DENSE_EVERY - 1:
-                                    r1 = min(rows, r0 + chunk_rows)
-                                    out[r0:r1].copy_(src[r0:r1], non_blocking=True)
-                                    stats["dense_chunks"] += 1
-                                    stats["h2d_bytes"] += (r1 - r0) * cols * 4
                     for ci, r0 in enumerate(range(0, rows, chunk_rows)):
                         r1 = min(rows, r0 + chunk_rows)
                         nnz = C.c_int64(-1)
                         if hybrid and not dense_mode and ci % PACK_DENSE_EVERY == PACK_DENSE_EVERY - 1:
+                            # this chunk crosses PCIe as it is, queued on its own stream in chunk order: the copy engine works
+                            # on it while the host cores pack the next chunks (their copies queue up behind it)
+                            with torch.cuda.stream(copy2):
+                                out[r0:r1].copy_(src[r0:r1], non_blocking=True)
+                            stats["dense_chunks"] += 1
+                            stats["h2d_bytes"] += (r1 - r0) * cols * 4
                             continue
                         if not dense_mode:
                             c = len(sent)
-                            slot, twin = slots[c % 2], twins[c % 2]
-                            if c >= 2:
-                                sent[c - 2].synchronize()
+                            slot, twin = slots[c % PACK_SLOTS], twins[c % PACK_SLOTS]
+                            if c >= PACK_SLOTS:
+                                sent[c - PACK_SLOTS].synchronize()
                             t_pack = time.perf_counter()
                             N.check(lib.n2v2r_host_pack_nonzeros(C.c_void_p(src[r0:r1].data_ptr()), r1 - r0, cols, cols,
                                                                  N.ptr(slot["bitmap"]), N.ptr(slot["values"]),
@@ -660,7 +681,7 @@ CONVERGED_STATUS = {0: "max_iters", 1: "converged", 2: "stagnated"}
 
 def uase(layers, k, l=64, tol=1e-5, max_iters=300, min_iters=2, seed=42, check_dims=None, algo=N.ALGO_TCGEN05,
          k_chunk=0, allreduce=None, T_global=None, layer_offset=0, want_left=False, cheb_degree=0, group=None,
-         floor_mult=0.0, rel_floor=0.0, first_degree=0, no_early_lock=False, trace=False):
+         floor_mult=0.0, rel_floor=0.0, first_degree=0, no_early_lock=False, trace=False, slab_group=None):
     """K3-K8: returns (embeddings (T_local, n, k) fp32 device, sigma (k,) float64, left | None, stats dict).
 
     stats["converged"] is the solver's tri-state (0 = max_iters reached, 1 = angle bound <= tol at every checked d or every
@@ -690,7 +711,17 @@ def uase(layers, k, l=64, tol=1e-5, max_iters=300, min_iters=2, seed=42, check_d
     arr = (N.Layer * T)(*[L.c_struct() for L in layers])
     state = None
     user = None
-    if allreduce is not None:
+    slabs = any(L.rows > 0 for L in layers)
+    if slabs:                                    # row slabs: Y over all ranks, Z_t over the ranks of this layer group
+        from . import dist
+        comm = dist.native_comm(group)
+        if comm is None:
+            raise RuntimeError("row-slab layers need torch.distributed on NCCL (the library issues the all-reduces itself)")
+        p.comm_mode = 1
+        user = comm
+        p.group_comm = dist.native_comm(slab_group) if slab_group is not None else comm
+        cb = C.cast(None, N.ALLREDUCE_FN)
+    elif allreduce is not None:
         cb = N.ALLREDUCE_FN(allreduce)
     elif (T_global or T) > T:                    # layer-sharded: all-reduce Y over the ranks (dist.py)
         from . import dist

@@ -80,9 +80,9 @@ class StabilityRun:
         local = []
         self.solver_infos = []
         self.batch_stats = []
-        # "seed_batch" (additive config key, default 3): that many solves run concurrently and share every pass over a layer,
+        # "seed_batch" (additive config key, default 6): that many solves run concurrently and share every pass over a layer,
         # three operands per pass (device.uase_batched); each solve is bit-identical to its unbatched run.  1 = one after the other.
-        group = max(1, min(16, int(cfg.get("seed_batch", 3))))
+        group = max(1, min(16, int(cfg.get("seed_batch", 6))))
         batchable = group > 1 and all(L.storage == "planes" for L in layers)
         for g0 in range(0, len(mine), group if batchable else 1):
             chunk = mine[g0:g0 + (group if batchable else 1)]

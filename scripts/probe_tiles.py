@@ -48,6 +48,20 @@ if "--cta2" in sys.argv:                        # the CTA-pair kernel (cta_group
         out["tiles_cta2_ms"] = ms_2
         out["cta2_bit_identical"] = bool(torch.equal(y_2.view(torch.int32), y_t.view(torch.int32)))
         out["cta2_max_abs_diff"] = float((y_2 - y_t).abs().max())
+        names2 = ["mma:wait_a_full", "mma:wait_x_full+peer", "mma:wait_tmem_empty", "-", "conv:wait_a_empty", "conv:restore", "conv:bar",
+                  "conv:wait_landing", "conv:scatter", "conv:fence+arrive"]
+        for mode, name in ((0, "full"), (1, "no_scatter"), (2, "no_mma"), (3, "skeleton")):
+            N.load().n2v2r__debug_sparse_mode(ctypes.c_int(mode))
+            out[f"cta2_ms_{name}"] = timed(Lt)[0]
+            clk = torch.zeros(148 * 16, dtype=torch.int64, device=dev)
+            N.load().n2v2r__debug_sparse_clk(ctypes.c_void_p(clk.data_ptr()))
+            D.layer_apply(Lt, x, ws=ws)
+            torch.cuda.synchronize()
+            N.load().n2v2r__debug_sparse_clk(ctypes.c_void_p(0))
+            c = clk.view(74, 2, 16).double().mean(dim=0).cpu().numpy()
+            out[f"cta2_cycles_{name}"] = {"leader": {nm: round(float(v)) for nm, v in zip(names2, c[0]) if nm != "-"},
+                                          "peer": {nm: round(float(v)) for nm, v in zip(names2, c[1]) if nm != "-" and not nm.startswith("mma")}}
+        N.load().n2v2r__debug_sparse_mode(ctypes.c_int(0))
     finally:
         N.load().n2v2r__debug_sparse_cta2(ctypes.c_int(0))
 if "--debug-modes" in sys.argv:                 # profiling: the kernel without its converters / without its MMAs (wrong results)
