@@ -72,6 +72,9 @@ def parse_args():
                          "expanded in shared memory for sparse layers; auto = the product default")
     ap.add_argument("--no-cross-check", action="store_true",
                     help="skip the untimed second solve (other seed, l = 80) whose subspace angle against the timed solve is reported")
+    ap.add_argument("--pack-dense-every", type=int, default=-1,
+                    help="e2e leg (development): every N-th row chunk of a pinned host graph crosses PCIe dense while the host packs the "
+                         "others (device.PACK_DENSE_EVERY); 0 = pack every chunk; -1 = the product default")
     ap.add_argument("--seed-batch", type=int, default=6,
                     help="workload c5: solves that run concurrently and share every pass over a layer (1 = one after the other)")
     ap.add_argument("--cpu-ladder", default="2000,4000,8000",
@@ -450,7 +453,8 @@ def transfer_note(x):
         return "dense float32 copies"
     return (f"packed on the host ({x['packed_chunks']} row chunks as bitmap + non-zero values, {x['dense_chunks']} dense"
             + (" on a second copy stream while the host cores pack" if x.get("hybrid") else "") + "; "
-            f"{x.get('threads', 0)} host threads, {x.get('pack_s', 0):.3f} s packing of {x.get('total_s', 0):.3f} s transfer + load pass), "
+            f"{x.get('threads', 0)} host threads, {x.get('pack_s', 0):.3f} s packing, producer thread done after {x.get('producer_s', 0):.3f} s, "
+            f"{x.get('total_s', 0):.3f} s transfer + load pass), "
             f"expanded on the device")
 
 
@@ -544,6 +548,9 @@ def cross_solve_check(layers, w, l, emb, bordas, T_global, layer_offset, gather,
 
 def run_b200_arm(args):
     w = workload_of(args)
+    if args.pack_dense_every >= 0:
+        from node2vec2rank_b200 import device as _D
+        _D.PACK_DENSE_EVERY = args.pack_dense_every
     if w.get("bipartite"):
         return run_b200_c4(args, w)
     if w.get("seeds"):

@@ -601,19 +601,26 @@ __global__ void __launch_bounds__(384, 1) sparse_mma_kernel(const __grid_constan
     int as = 0, ls = 0; uint32_t pa = 0, pl = 0;
     uint32_t prev0 = 0, prev1 = 0, prev2 = 0, prev3 = 0;   // entries scattered into each A stage by its previous use
     unsigned long long dbg[6] = {0, 0, 0, 0, 0, 0};
+    // kernel parameters the loops need, in registers (left in the constant bank they cost a dependent load per store);
+    // planes that are not issued alias plane 0's address and are simply not written
+    const uint32_t pb1 = a.n_planes > 1 ? a.a_plane_bytes : 0u, pb2 = a.n_planes > 2 ? 2u * a.a_plane_bytes : 0u;
+    const bool has1 = a.n_planes > 1, has2 = a.n_planes > 2;
+    const uint32_t stage_bytes = a.a_stage_bytes, land_off = a.off_land, undo_off = a.off_undo;
+    const int n_as = a.a_stages, n_ls = a.l_slots;
+    const bool skip_scatter = (a.debug_mode & 1) != 0;
     for (int u = cid; u < n_units; u += ncl) {
       const int split = u / n_st;
       const int kb0 = split * a.kb_per_split, kb1 = min(a.n_kb, kb0 + a.kb_per_split);
       for (int kb = kb0; kb < kb1; ++kb) {
-        const uint32_t abase = smem0 + as * a.a_stage_bytes;
-        const uint32_t undo = smem0 + a.off_undo + as * (kUndoCap * 2);
+        const uint32_t abase = smem0 + as * stage_bytes;
+        const uint32_t undo = smem0 + undo_off + as * (kUndoCap * 2);
         const uint32_t prev = as == 0 ? prev0 : as == 1 ? prev1 : as == 2 ? prev2 : prev3;
         const long long c0 = clock64();
         mbar_wait(bar_aempty + 8 * as, pa ^ 1u);        // the MMAs that read this stage have retired
         const long long c1 = clock64();
-        if (a.debug_mode & 1) {
+        if (skip_scatter) {
         } else if (prev > (uint32_t)kUndoCap) {
-          for (uint32_t i = ct; i < (a.a_stage_bytes >> 4); i += 128) st_shared_zero16(abase + (i << 4));
+          for (uint32_t i = ct; i < (stage_bytes >> 4); i += 128) st_shared_zero16(abase + (i << 4));
         } else {
           for (uint32_t i = 4 * ct; i < prev; i += 512) {        // 4 remembered positions per thread and round: one 8-byte load
             const uint2 pp = ld_shared_v2(undo + 2 * i);
@@ -621,9 +628,10 @@ __global__ void __launch_bounds__(384, 1) sparse_mma_kernel(const __grid_constan
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
               if (ps[e] != kPosSkip) {
-                st_shared_u16(abase + 2 * ps[e], 0u);
-                if (a.n_planes > 1) st_shared_u16(abase + a.a_plane_bytes + 2 * ps[e], 0u);
-                if (a.n_planes > 2) st_shared_u16(abase + 2 * a.a_plane_bytes + 2 * ps[e], 0u);
+                const uint32_t ad = abase + 2 * ps[e];
+                st_shared_u16(ad, 0u);
+                if (has1) st_shared_u16(ad + pb1, 0u);
+                if (has2) st_shared_u16(ad + pb2, 0u);
               }
             }
           }
@@ -639,9 +647,9 @@ __global__ void __launch_bounds__(384, 1) sparse_mma_kernel(const __grid_constan
           wl += clock64() - w0;
           const uint32_t c = lcnt[ls];
           const uint32_t nent = c & 0x7fffffffu;         // a multiple of 4, at most kLandCap = 4 x 128
-          const uint32_t land = smem0 + a.off_land + ls * (kLandCap * 8);
+          const uint32_t land = smem0 + land_off + ls * (kLandCap * 8);
           const uint32_t j = 4 * ct;
-          if (!(a.debug_mode & 1) && j < nent) {         // this thread's 4 entries of the chunk: one 32-byte load
+          if (!skip_scatter && j < nent) {         // this thread's 4 entries of the chunk: one 32-byte load
             const uint4 e01 = ld_shared_v4(land + 8 * j), e23 = ld_shared_v4(land + 8 * j + 16);
             const uint32_t ex[4] = {e01.x, e01.z, e23.x, e23.z}, ey[4] = {e01.y, e01.w, e23.y, e23.w};
             if (total + j < (uint32_t)kUndoCap)
@@ -650,15 +658,16 @@ __global__ void __launch_bounds__(384, 1) sparse_mma_kernel(const __grid_constan
             for (int e = 0; e < 4; ++e) {
               const uint32_t pos = ex[e] & 0xFFFFu;
               if (pos != kPosSkip) {
-                st_shared_u16(abase + 2 * pos, ex[e] >> 16);
-                if (a.n_planes > 1) st_shared_u16(abase + a.a_plane_bytes + 2 * pos, ey[e] & 0xFFFFu);
-                if (a.n_planes > 2) st_shared_u16(abase + 2 * a.a_plane_bytes + 2 * pos, ey[e] >> 16);
+                const uint32_t ad = abase + 2 * pos;
+                st_shared_u16(ad, ex[e] >> 16);
+                if (has1) st_shared_u16(ad + pb1, ey[e] & 0xFFFFu);
+                if (has2) st_shared_u16(ad + pb2, ey[e] >> 16);
               }
             }
           }
           mbar_arrive(bar_lempty + 8 * ls);
           total += nent;
-          if (++ls == a.l_slots) { ls = 0; pl ^= 1u; }
+          if (++ls == n_ls) { ls = 0; pl ^= 1u; }
           if (c & 0x80000000u) break;
         }
         if (as == 0) prev0 = total; else if (as == 1) prev1 = total; else if (as == 2) prev2 = total; else prev3 = total;
@@ -669,7 +678,7 @@ __global__ void __launch_bounds__(384, 1) sparse_mma_kernel(const __grid_constan
           const long long c5 = clock64();
           dbg[0] += c1 - c0; dbg[1] += c2 - c1; dbg[2] += c3 - c2; dbg[3] += wl; dbg[4] += (c4 - c3) - wl; dbg[5] += c5 - c4;
         }
-        if (++as == a.a_stages) { as = 0; pa ^= 1u; }
+        if (++as == n_as) { as = 0; pa ^= 1u; }
       }
     }
     if (a.debug_clk && ct == 0) { for (int i = 0; i < 6; ++i) a.debug_clk[blockIdx.x * 16 + 4 + i] = dbg[i]; }

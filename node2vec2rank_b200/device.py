@@ -409,9 +409,10 @@ PACK_MIN_ENTRIES = 4_000_000          # below this a layer crosses PCIe dense (t
 PACK_CHUNK_ENTRIES = 300_000_000      # rows are packed and copied in chunks of about this many entries
 PACK_MAX_DENSITY = 0.3                # staging capacity for the non-zero values, as a fraction of a chunk's entries
 PACK_SLOTS = 3                        # pinned staging slots: packed chunks in flight behind a dense chunk on the copy engine
-PACK_DENSE_EVERY = 4                  # pinned sources: every 4th row chunk crosses PCIe dense on its own stream while the host
-                                      # cores pack the others (packing runs at ~150 GB/s of host reads, the otherwise idle copy
-                                      # engine adds ~55 GB/s); 0 = pack every chunk
+PACK_DENSE_EVERY = 0                  # N > 1 (pinned sources): every N-th row chunk crosses PCIe dense on its own stream while the
+                                      # host cores pack the others.  Measured at C3 (profiles/README.md): with N = 4 the DMA reads
+                                      # compete with the packing threads for host memory bandwidth and the step gets SLOWER
+                                      # (transfer 0.73 s against 0.57 s), so every chunk is packed (0) by default
 _pack_staging = {}                    # (chunk_rows, cols) -> two pinned staging slots, kept across calls (pinning is slow)
 
 
