@@ -38,6 +38,9 @@ WORKLOADS = {
     # BASELINE.json configs[2]: the configuration the metric is quoted on (fits one B200: 80 GB of planes)
     "c3": dict(n=50000, T=8, K=32, weighted=True, keep=10, binarize=False, strategy="one_vs_rest",
                name="synthetic 8-layer weighted SBM n=50k, top_percent_keep=10, one_vs_rest, d=4..24, euclidean+cosine, Borda"),
+    # the same with 24-bit weights fp32(u') + 2^-24: three bf16 plane terms are needed for exactness
+    "c3w24": dict(n=50000, T=8, K=32, weighted=2, keep=10, binarize=False, strategy="one_vs_rest",
+                  name="synthetic 8-layer SBM with 24-bit weights n=50k, top_percent_keep=10, one_vs_rest, d=4..24, euclidean+cosine, Borda"),
     # BASELINE.json configs[1]
     "c2": dict(n=20000, T=2, K=32, weighted=False, keep=100, binarize=True, strategy="sequential",
                name="synthetic 2-layer dense SBM n=20k, binarize, sequential, d=4..24, euclidean+cosine, Borda"),

@@ -62,7 +62,8 @@ int n2v2r_device_info(int device, int* sm_count, int* cc, size_t* total_mem);
  * Counter-based: entry (i,j), i<j, of layer `layer` is a pure function of
  * (seed, layer, i, j); A[j,i] = A[i,j]; zero diagonal.  community(i) = i % K.
  * h_B is the K*K row-major (symmetric) block probability matrix on the HOST.
- * weighted=0: A in {0,1}; weighted=1: A = edge * w, w in (0,1] a second counter draw.
+ * weighted=0: A in {0,1}; weighted=1: A = edge * w, w in (0,1] a second counter draw with 16 bits ((k+1)/65536: two bf16
+ * planes are exact); weighted=2: 24-bit weights fp32(u') + 2^-24 (three planes).
  * NumPy twin: node2vec2rank_b200/synthetic.py (bit-identical).
  * ---------------------------------------------------------------------------------- */
 int n2v2r_sbm_generate(void* stream, float* d_out, int64_t n, int64_t ld, int K,

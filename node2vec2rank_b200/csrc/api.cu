@@ -56,7 +56,10 @@ __global__ void __launch_bounds__(256) sbm_kernel(float* __restrict__ out, int64
         const uint64_t h = hash4(seed, (uint64_t)layer, a, b);
         const float p = sB[zi * K + (int)(j % K)];
         if (u24(h) < p) {
-          if (weighted) {
+          if (weighted == 2) {
+            const uint64_t h2 = mix64(h ^ 0xA5A5A5A5A5A5A5A5ull);
+            x = u24(h2) + (1.0f / 16777216.0f);                            // 24-bit weight fp32(u') + 2^-24 in (0,1]
+          } else if (weighted) {
             const uint64_t h2 = mix64(h ^ 0xA5A5A5A5A5A5A5A5ull);
             x = (float)((uint32_t)(h2 >> 48) + 1u) * (1.0f / 65536.0f);   // 16-bit weight in (0,1]
           } else {

@@ -39,7 +39,11 @@ def sbm_layer_numpy(n, K, B, seed, layer, weighted=False, rows=None):
         u = (h >> np.uint64(40)).astype(np.uint32).astype(np.float32) * np.float32(1.0 / 16777216.0)
         p = B[(I % K), (J % K)]
         edge = (u < p) & (I != J)
-        if weighted:
+        if weighted == 2:                 # 24-bit weights fp32(u') + 2^-24
+            h2 = _mix64(h ^ np.uint64(0xA5A5A5A5A5A5A5A5))
+            w = (h2 >> np.uint64(40)).astype(np.uint32).astype(np.float32) * np.float32(1.0 / 16777216.0) + np.float32(1.0 / 16777216.0)
+            out = np.where(edge, w, np.float32(0))
+        elif weighted:
             h2 = _mix64(h ^ np.uint64(0xA5A5A5A5A5A5A5A5))
             w = ((h2 >> np.uint64(48)).astype(np.uint32) + np.uint32(1)).astype(np.float32) * np.float32(1.0 / 65536.0)
             out = np.where(edge, w, np.float32(0))

@@ -17,7 +17,7 @@ def _t(a, gpu):
 
 
 # ---- K0 ---------------------------------------------------------------------------------------
-@pytest.mark.parametrize("weighted", [False, True])
+@pytest.mark.parametrize("weighted", [False, True, 2])
 def test_sbm_generator_matches_numpy_twin(gpu, weighted):
     from node2vec2rank_b200 import device as D
     from node2vec2rank_b200.synthetic import block_matrices, sbm_layer_numpy
