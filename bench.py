@@ -815,8 +815,10 @@ def run_b200_c5(args, w):
     layers, host_graphs = [], []
     for t in range(T):
         raw = D.sbm_generate(n, K, Bs[t], seed=GRAPH_SEED, layer=t, weighted=w["weighted"])
+        # seed batching multiplies bf16 planes (three operands per pass); e4m3 layers are served one solve at a time
+        c5_storage = "planes" if (args.layer_storage == "auto" and args.seed_batch > 1) else args.layer_storage
         layer, f32 = D.preprocess_to_layer(raw, top_percent_keep=w["keep"], binarize=w["binarize"], want_f32=not args.no_e2e,
-                                           storage=args.layer_storage)
+                                           storage=c5_storage)
         del raw
         if f32 is not None:
             h = torch.empty((n, n), dtype=torch.float32, pin_memory=True)

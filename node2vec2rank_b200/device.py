@@ -320,7 +320,8 @@ def project(W: torch.Tensor, on):
     return out
 
 
-E4M3_AUTO = False               # storage="auto": binarised layers as one e4m3 plane (set after measuring, see profiles/)
+E4M3_AUTO = True                # storage="auto": large binarised layers are held as one e4m3 plane (C2: 9-16 % faster steps than
+                                # the bf16 plane, profiles/README.md).  Seed batching needs bf16 planes: pass storage="planes"
 def make_slab_layer(x32: torch.Tensor, row_offset: int, rows: int, n_planes=None):
     """Row slab of a layer for sharding ONE layer over several GPUs (fewer layers than GPUs): x32 is the (n, n)
     fp32 device matrix (or just its rows [row_offset, row_offset + rows)); the slab and its transpose are stored as bf16
@@ -400,9 +401,16 @@ def make_layer(x32: torch.Tensor, n_planes=None, colsum=None, check_symmetry=Tru
                 layer.colsum = x32.sum(dim=0, dtype=torch.float64)
             return layer
         n_planes = n_planes or P
+    explicit_planes = n_planes is not None and known_sym is None
     P = n_planes or planes_needed(x32)
     _, planes, ld_p, cs = transform(x32, n_planes=P, want_colsum=colsum is None)
-    return finish_layer(planes, n, ld_p, P, cs if colsum is None else colsum, check_symmetry, known_symmetric=known_sym)
+    layer = finish_layer(planes, n, ld_p, P, cs if colsum is None else colsum, check_symmetry, known_symmetric=known_sym)
+    if storage == "auto" and E4M3_AUTO and P == 1 and n >= TILES_MIN_N and not explicit_planes:
+        try:
+            layer = layer.to_e4m3()            # one-plane layers whose values e4m3 holds exactly (binarised): half the bytes
+        except ValueError:
+            pass
+    return layer
 
 
 PACK_MIN_ENTRIES = 4_000_000          # below this a layer crosses PCIe dense (the packed pipeline has fixed costs)

@@ -44,6 +44,8 @@ class StabilityRun:
         if not self.seeds:
             raise ValueError("at least one seed is needed")
         self.config = dict(config)
+        if int(self.config.get("seed_batch", 6)) > 1 and self.config.get("layer_storage", "auto") == "auto":
+            self.config["layer_storage"] = "planes"       # seed batching multiplies bf16 planes (three operands per layer pass)
         self.node_names = nodes
         self._model = N2V2R(graphs=graphs, nodes=nodes, config=self.config)
         self.save_dir = self._model.save_dir

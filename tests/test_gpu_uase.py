@@ -167,7 +167,7 @@ def test_full_size_c2_properties(gpu):
         raw = D.sbm_generate(n, K, Bs[t], seed=1, layer=t)
         layers.append(D.preprocess_to_layer(raw, binarize=True)[0])
         del raw
-    assert all(L.n_planes == 1 and L.symmetric for L in layers)
+    assert all(L.n_planes == 1 and L.symmetric and L.storage == "e4m3" for L in layers)     # binarised: one e4m3 plane
     dims = list(range(4, 25, 2))
     emb, sigma, left, info = D.uase(layers, k, l=l, seed=42, check_dims=dims, want_left=True)
     assert info["converged"] and info["iterations"] <= 40, info
@@ -183,8 +183,10 @@ def test_full_size_c2_properties(gpu):
     pad[:, :k] = U
     MU = torch.zeros_like(pad)
     for L in layers:
-        z = D.layer_apply(L, pad, transpose=True, algo=N.ALGO_SIMT)
-        MU += D.layer_apply(L, z, transpose=False, algo=N.ALGO_SIMT)
+        Lp = D.make_layer(L.to_dense(), storage="planes", n_planes=1, check_symmetry=False)     # the SIMT product reads bf16 planes
+        z = D.layer_apply(Lp, pad, transpose=True, algo=N.ALGO_SIMT)
+        MU += D.layer_apply(Lp, z, transpose=False, algo=N.ALGO_SIMT)
+        del Lp
     lam = torch.from_numpy(sigma ** 2).to(gpu)
     r = (MU[:, :k].double() - U.double() * lam).norm(dim=0) / lam
     assert float(r.max()) <= 2e-5, r
