@@ -82,7 +82,7 @@ def parse_args():
                     help="workload c5: solves that run concurrently and share every pass over a layer (1 = one after the other)")
     ap.add_argument("--cpu-ladder", default="2000,4000,8000",
                     help="--impl reference: node counts the reference path is timed at (all layers), ascending")
-    ap.add_argument("--cpu-budget-s", type=float, default=420.0, help="--impl reference: wall-clock budget of the ladder")
+    ap.add_argument("--cpu-budget-s", type=float, default=330.0, help="--impl reference: wall-clock budget of the ladder")
     return ap.parse_args()
 
 

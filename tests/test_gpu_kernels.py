@@ -197,7 +197,7 @@ def test_layer_apply_tcgen05_vs_fp64(gpu, n, l, planes):
         a = a.astype(np.float32)
     else:
         a = (rng.random((n, n)).astype(np.float32)) * (rng.random((n, n)) < 0.3).astype(np.float32)
-    L = D.make_layer(_t(a, gpu))
+    L = D.make_layer(_t(a, gpu), storage="planes")          # the dense-plane kernels (tiles / e4m3 have their own tests)
     assert L.n_planes == planes
     x = rng.normal(size=(n, l)).astype(np.float32)
     xd = _t(x, gpu)
