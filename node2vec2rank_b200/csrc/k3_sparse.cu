@@ -17,57 +17,10 @@
 // Replaces the same reference code as k3_tcgen05.cu: the ARPACK operator matvec / rmatvec (scipy _svds.py:442-457)
 // under spectral_embedding.UASE (model.py:54-55); the compressed form plays the role of the reference's
 // csc_matrix conversion (model.py:51-53).
-#include "k5_orth.cuh"
-#include "tc_ptx.cuh"
+#include "sparse_common.cuh"
 #include <algorithm>
 
 namespace n2v2r {
-
-constexpr int kLandCap = 512;        // entries per landing slot (4 KB)
-constexpr int kUndoCap = 2048;       // positions remembered per A stage; a denser tile pair is cleared as a whole
-constexpr int kSortCap = 2048;        // tile lists up to this length are written in bank-interleaved order (builder)
-constexpr uint32_t kPosSkip = 0xFFFFu;   // padding entry (tile lists are padded to a multiple of 4 entries = 32 bytes)
-
-// element offset of (row r, column c) inside one K-major SWIZZLE_128B plane of a (tile_rows x 64) bf16 tile
-__host__ __device__ __forceinline__ uint32_t swz_pos(int r, int c) {
-  return (uint32_t)(((r >> 3) << 9) + ((r & 7) << 6) + ((((c >> 3) ^ (r & 7))) << 3) + (c & 7));
-}
-__host__ __device__ __forceinline__ void swz_inv(uint32_t pos, int* r, int* c) {
-  const int rr = (pos >> 6) & 7;
-  *r = (int)((pos >> 9) << 3) + rr;
-  *c = (int)(((((pos >> 3) & 7) ^ rr) << 3) + (pos & 7));
-}
-
-__device__ __forceinline__ void bulk_copy_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-               ::"r"(dst), "l"(src), "r"(bytes), "r"(bar)
-               : "memory");
-}
-__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void st_shared_u16(uint32_t addr, uint32_t v) {
-  asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"((unsigned short)v) : "memory");
-}
-__device__ __forceinline__ uint32_t ld_shared_u16(uint32_t addr) {
-  unsigned short v;
-  asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(addr));
-  return v;
-}
-__device__ __forceinline__ uint2 ld_shared_v2(uint32_t addr) {
-  uint2 v;
-  asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
-  return v;
-}
-__device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
-  uint4 v;
-  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
-  return v;
-}
-__device__ __forceinline__ void st_shared_v2(uint32_t addr, uint32_t a, uint32_t b) {
-  asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(addr), "r"(a), "r"(b) : "memory");
-}
-__device__ __forceinline__ void st_shared_zero16(uint32_t addr) {
-  asm volatile("st.shared.v4.u32 [%0], {%1, %1, %1, %1};" ::"r"(addr), "r"(0u) : "memory");
-}
 
 // ---- CTA-pair (cta_group::2) helpers -------------------------------------------------------------------
 __device__ __forceinline__ uint32_t cluster_ctarank() {
@@ -695,6 +648,9 @@ __global__ void __launch_bounds__(384, 1) sparse_mma_kernel(const __grid_constan
 
 // ---- host ---------------------------------------------------------------------------------------
 static int g_sparse_debug_mode = 0;
+static int g_sparse_ts = 0;              // 1 = A tile in tensor memory (k3_sparse_ts.cu); switched by n2v2r__debug_sparse_ts
+int stream_apply_tiles_ts(cudaStream_t s, const StreamPlan& plan, const uint32_t* tile_ptr, const void* entries, int n_planes,
+                          int tile_rows, const float* x, __nv_bfloat16* xs, float* parts, float* out, int accumulate);
 static int g_sparse_cta2 = 0;            // 1 = pair kernel (cta_group::2); switched by n2v2r__debug_sparse_cta2 until it is the default
 static unsigned long long* g_sparse_debug_clk = nullptr;
 // K split that balances (row tiles x splits) units over the persistent CTAs
@@ -717,6 +673,8 @@ int stream_apply_tiles(cudaStream_t s, const StreamPlan& plan, const uint32_t* t
   N2V2R_REQUIRE(xs && parts && tile_ptr && entries, "compressed-tile product needs its workspace and the tile lists");
   N2V2R_REQUIRE(tile_rows == 128 || tile_rows == 256, "compressed tiles: tile_rows must be 128 or 256");
   N2V2R_REQUIRE(n_planes >= 1 && n_planes <= 3, "compressed tiles: 1..3 planes");
+  if (g_sparse_ts && (512 - (tile_rows / 128) * 3 * plan.l) >= (tile_rows / 128) * n_planes * 32 && !(tile_rows == 256 && n_planes == 3))
+    return stream_apply_tiles_ts(s, plan, tile_ptr, entries, n_planes, tile_rows, x, xs, parts, out, accumulate);
   int rc = launch_split_transpose(s, x, plan.n, plan.l, plan.n_pad, xs);
   if (rc) return rc;
   SparseArgs a;
@@ -831,6 +789,7 @@ using namespace n2v2r;
 extern "C" void n2v2r__debug_sparse_mode(int mode) { g_sparse_debug_mode = mode; }
 extern "C" void n2v2r__debug_sparse_clk(void* d_buf) { g_sparse_debug_clk = (unsigned long long*)d_buf; }
 extern "C" void n2v2r__debug_sparse_cta2(int on) { g_sparse_cta2 = on; }
+extern "C" void n2v2r__debug_sparse_ts(int on) { g_sparse_ts = on; }
 
 // ---- C ABI: building the compressed tiles --------------------------------------------------------
 extern "C" int n2v2r_tiles_count(void* stream, const float* d_in, int64_t n, int64_t ld, uint32_t* d_counts, uint32_t* d_counts_t,

@@ -344,7 +344,7 @@ TILES_MAX_DENSITY = 0.08        # layers sparser than this are stored as compres
 TILES_MIN_N = 4096              # ... when they are large enough for the streaming product to matter
 
 
-def make_tiles_layer(x32: torch.Tensor, colsum=None, max_density=None):
+def make_tiles_layer(x32: torch.Tensor, colsum=None, max_density=None, tile_rows=None):
     """fp32 (n, n) device matrix -> DeviceLayer(storage="tiles"), or (None, planes, symmetric) when the matrix is denser
     than `max_density` (the caller then builds planes; the count pass has already told it how many and the symmetry)."""
     lib = N.load()
@@ -359,7 +359,9 @@ def make_tiles_layer(x32: torch.Tensor, colsum=None, max_density=None):
     N.check(lib.n2v2r_tiles_count(N.stream_ptr(), N.ptr(x32), n, x32.stride(0), N.ptr(counts[0]), N.ptr(counts[1]),
                                   C.byref(planes), C.byref(sym)))
     P = planes.value
-    tile_rows = 256 if P <= 2 else 128
+    tile_rows = int(tile_rows) if tile_rows else (256 if P <= 2 else 128)
+    if tile_rows not in (128, 256) or (tile_rows == 256 and P == 3):
+        raise ValueError("tile_rows must be 128 or 256 (128 for three-plane layers)")
     n_tiles = ((n + tile_rows - 1) // tile_rows) * n_kb
 
     def build(which, transpose):

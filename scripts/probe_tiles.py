@@ -40,6 +40,25 @@ def timed(layer, k_chunk=0):
 
 ms_t, y_t = timed(Lt)
 out["tiles_ms"] = ms_t
+if "--ts" in sys.argv:                          # A tile in tensor memory (k3_sparse_ts.cu) against the shared-memory kernel
+    import ctypes
+    variants = [("tr256", Lt)]
+    if Lt.n_planes <= 2:
+        L128, _, _ = D.make_tiles_layer(f32, tile_rows=128)
+        variants.append(("tr128", L128))
+    for nm, Lx in variants:
+        y_ss = timed(Lx)[1] if nm != "tr256" else y_t
+        if nm != "tr256":
+            out[f"tiles_{nm}_ms"] = timed(Lx)[0]
+        N.load().n2v2r__debug_sparse_ts(ctypes.c_int(1))
+        try:
+            ms_ts, y_ts = timed(Lx)
+            out[f"ts_{nm}_ms"] = ms_ts
+            out[f"ts_{nm}_bit_identical"] = bool(torch.equal(y_ts.view(torch.int32), y_ss.view(torch.int32)))
+            out[f"ts_{nm}_max_abs_diff"] = float((y_ts - y_ss).abs().max())
+            out[f"ts_{nm}_ref_max"] = float(y_ss.abs().max())
+        finally:
+            N.load().n2v2r__debug_sparse_ts(ctypes.c_int(0))
 if "--cta2" in sys.argv:                        # the CTA-pair kernel (cta_group::2) against the one-CTA kernel
     import ctypes
     N.load().n2v2r__debug_sparse_cta2(ctypes.c_int(1))
