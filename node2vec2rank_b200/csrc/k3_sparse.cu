@@ -673,7 +673,7 @@ int stream_apply_tiles(cudaStream_t s, const StreamPlan& plan, const uint32_t* t
   N2V2R_REQUIRE(xs && parts && tile_ptr && entries, "compressed-tile product needs its workspace and the tile lists");
   N2V2R_REQUIRE(tile_rows == 128 || tile_rows == 256, "compressed tiles: tile_rows must be 128 or 256");
   N2V2R_REQUIRE(n_planes >= 1 && n_planes <= 3, "compressed tiles: 1..3 planes");
-  if (g_sparse_ts && (512 - (tile_rows / 128) * 3 * plan.l) >= (tile_rows / 128) * n_planes * 32 && !(tile_rows == 256 && n_planes == 3))
+  if (g_sparse_ts && (512 - (tile_rows / 128) * 3 * plan.l) / (n_planes * 32) >= tile_rows / 128 && !(tile_rows == 256 && n_planes == 3))
     return stream_apply_tiles_ts(s, plan, tile_ptr, entries, n_planes, tile_rows, x, xs, parts, out, accumulate);
   int rc = launch_split_transpose(s, x, plan.n, plan.l, plan.n_pad, xs);
   if (rc) return rc;

@@ -6,7 +6,9 @@
 // undo list), then every converter thread reads ITS OWN ROW of the tile back (8 x 16 bytes per plane, conflict-free in the
 // swizzled layout), writes it into tensor memory with tcgen05.st (lane = row, one 32-bit column = two consecutive k) and
 // restores the zeros at once; the MMAs take A from TMEM and only the split operand from shared memory.  The shared-memory
-// tile is free again as soon as it has been read, so what rings is the TMEM copy of A (`ta` stages next to the accumulators).
+// tile is free again as soon as it has been read, so what rings is the TMEM copy of A: slots of ONE 128-row half each (P x 32
+// columns) next to the accumulators, filled by the converter group of that half (128 threads per half: warps 8-11 own the rows
+// of half 0, warps 12-15 those of half 1) and released half by half as the MMAs retire.
 // Same entry format, same K split and MMA order as k3_sparse.cu: the product has the same bits.
 #include "sparse_common.cuh"
 #include <algorithm>
@@ -31,10 +33,21 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t* v) {
         "r"(v[30]), "r"(v[31])
       : "memory");
 }
+template <int N>
+__device__ __forceinline__ void conv_bar() {
+  if (N == 128) asm volatile("bar.sync 1, 128;" ::: "memory");
+  else asm volatile("bar.sync 1, 256;" ::: "memory");
+}
+__device__ __forceinline__ void st_shared_u32(uint32_t addr, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory"); }
+__device__ __forceinline__ uint32_t ld_shared_u32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
 struct SparseTsArgs {
-  int l, x_stages, l_slots, ta_stages;
+  int l, x_stages, l_slots, ta_slots;       // ta_slots: TMEM A slots of one 128-row half each
   int n_tiles, n_splits, kb_per_split, n_kb;
   int64_t rows_valid, out_ld, split_stride;
   uint32_t a_plane_bytes, a_buf_bytes, x_bytes;
@@ -46,7 +59,7 @@ struct SparseTsArgs {
 
 // MH = 128-row halves per tile (tile_rows / 128), P = bf16 plane terms.  Warp roles as in sparse_mma_kernel.
 template <int MH, int P>
-__global__ void __launch_bounds__(384, 1) sparse_ts_kernel(const __grid_constant__ CUtensorMap mapX, const SparseTsArgs a) {
+__global__ void __launch_bounds__(256 + 128 * MH, 1) sparse_ts_kernel(const __grid_constant__ CUtensorMap mapX, const SparseTsArgs a) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bars[40];
   __shared__ uint32_t tmem_base_smem;
@@ -54,19 +67,20 @@ __global__ void __launch_bounds__(384, 1) sparse_ts_kernel(const __grid_constant
   const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t bar_xfull = smem_u32(&bars[0]), bar_xempty = smem_u32(&bars[8]);
-  const uint32_t bar_tafull = smem_u32(&bars[16]), bar_taempty = smem_u32(&bars[20]);
+  const uint32_t bar_tafull = smem_u32(&bars[16]), bar_taempty = smem_u32(&bars[20]);    // up to 4 slots
   const uint32_t bar_lfull = smem_u32(&bars[24]), bar_lempty = smem_u32(&bars[32]);
   __shared__ __align__(8) uint64_t tbars[2];
   const uint32_t bar_tfull = smem_u32(&tbars[0]), bar_tempty = smem_u32(&tbars[1]);
   const int n_units = a.n_tiles * a.n_splits;
   const int nacc = 3 * a.l;
-  constexpr int kStageCols = MH * P * 32;                // TMEM columns of one A stage: per half and plane 64 k = 32 columns
+  constexpr int kSlotCols = P * 32;                      // TMEM columns of one A slot: one half, per plane 64 k = 32 columns
+  constexpr int kConv = 128 * MH;                        // converter threads
   const uint32_t a_col0 = (uint32_t)(MH * nacc);         // the A ring follows the accumulators
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < a.x_stages; ++i) { mbar_init(bar_xfull + 8 * i, 1); mbar_init(bar_xempty + 8 * i, 1); }
-    for (int i = 0; i < a.ta_stages; ++i) { mbar_init(bar_tafull + 8 * i, 128); mbar_init(bar_taempty + 8 * i, 1); }
-    for (int i = 0; i < a.l_slots; ++i) { mbar_init(bar_lfull + 8 * i, 1); mbar_init(bar_lempty + 8 * i, 128); }
+    for (int i = 0; i < a.ta_slots; ++i) { mbar_init(bar_tafull + 8 * i, 128); mbar_init(bar_taempty + 8 * i, 1); }
+    for (int i = 0; i < a.l_slots; ++i) { mbar_init(bar_lfull + 8 * i, 1); mbar_init(bar_lempty + 8 * i, kConv); }
     mbar_init(bar_tfull, 1);
     mbar_init(bar_tempty, 4);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -106,31 +120,31 @@ __global__ void __launch_bounds__(384, 1) sparse_ts_kernel(const __grid_constant
       tc_fence_after();
       bool first = true;
       for (int kb = kb0; kb < kb1; ++kb) {
-        mbar_wait(bar_tafull + 8 * ta, pta);
         mbar_wait(bar_xfull + 8 * xs, px);
-        tc_fence_after();
-        if (lane == 0) {
-          const uint32_t xbase = smem0 + a.off_x + xs * a.x_bytes;
-          const uint32_t abase = tmem_base + a_col0 + (uint32_t)(ta * kStageCols);
+        const uint32_t xbase = smem0 + a.off_x + xs * a.x_bytes;
 #pragma unroll
-          for (int h = 0; h < MH; ++h) {
+        for (int h = 0; h < MH; ++h) {
+          mbar_wait(bar_tafull + 8 * ta, pta);           // this half's rows are in its TMEM slot
+          tc_fence_after();
+          if (lane == 0) {
+            const uint32_t abase = tmem_base + a_col0 + (uint32_t)(ta * kSlotCols);
             bool acc = !first;
 #pragma unroll
             for (int p = 0; p < P; ++p) {
               const uint32_t idesc = idesc_bf16((3 - p) * a.l);
 #pragma unroll
               for (int k = 0; k < 4; ++k) {
-                umma_bf16_ts(tmem_base + h * nacc, abase + (uint32_t)((h * P + p) * 32 + k * 8), sw128_desc(xbase + k * 32), idesc, acc ? 1u : 0u);
+                umma_bf16_ts(tmem_base + h * nacc, abase + (uint32_t)(p * 32 + k * 8), sw128_desc(xbase + k * 32), idesc, acc ? 1u : 0u);
                 acc = true;
               }
             }
+            umma_commit(bar_taempty + 8 * ta);         // this TMEM slot may be overwritten
+            if (h == MH - 1) umma_commit(bar_xempty + 8 * xs);
           }
-          umma_commit(bar_taempty + 8 * ta);           // this TMEM copy of A may be overwritten
-          umma_commit(bar_xempty + 8 * xs);
+          __syncwarp();
+          if (++ta == a.ta_slots) { ta = 0; pta ^= 1u; }
         }
-        __syncwarp();
         first = false;
-        if (++ta == a.ta_stages) { ta = 0; pta ^= 1u; }
         if (++xs == a.x_stages) { xs = 0; px ^= 1u; }
       }
       if (lane == 0) umma_commit(bar_tfull);
@@ -211,11 +225,14 @@ __global__ void __launch_bounds__(384, 1) sparse_ts_kernel(const __grid_constant
     }
   } else if (warp >= 8) {
     // ===== converters: entry lists -> zeroed SWIZZLE_128B staging tile -> own row -> tensor memory =====
-    const int ct = threadIdx.x - 256;                  // 0..127 = row of each 128-row half this thread owns
-    const int q = warp & 3;                            // TMEM lane quarter of this warp (warps 8..11 -> 0..3)
-    int ls = 0, ta = 0, buf = 0; uint32_t pl = 0, pta = 0;
+    const int ct = threadIdx.x - 256;                  // 0 .. 128 MH - 1
+    const int hh = ct >> 7;                            // the 128-row half whose rows this thread's warp group owns
+    const int rr = ct & 127;                           // row inside the half = TMEM lane
+    const int q = warp & 3;                            // TMEM lane quarter of this warp
+    int ls = 0, buf = 0; uint32_t pl = 0;
+    long it = hh;                                      // running index of this group's (k block, half) items: it = i MH + hh
     const uint32_t pb = a.a_plane_bytes, buf_bytes = a.a_buf_bytes, land_off = a.off_land, undo_off = a.off_undo;
-    const int n_ls = a.l_slots, n_ta = a.ta_stages;
+    const int n_ls = a.l_slots, n_ta = a.ta_slots;
     for (int u = blockIdx.x; u < n_units; u += gridDim.x) {
       const int split = u / a.n_tiles;
       const int kb0 = split * a.kb_per_split, kb1 = min(a.n_kb, kb0 + a.kb_per_split);
@@ -223,20 +240,30 @@ __global__ void __launch_bounds__(384, 1) sparse_ts_kernel(const __grid_constant
         const uint32_t abase = smem0 + buf * buf_bytes;
         const uint32_t undo = smem0 + undo_off + buf * (kUndoCap * 2);
         // ---- 1. scatter this k block's entries into the (zero) staging tile, remembering the positions
+        constexpr int EPT = 512 / kConv;               // entries per thread and chunk: 4 (128 converters) or 2 (256)
         uint32_t total = 0;
         while (true) {
           mbar_wait(bar_lfull + 8 * ls, pl);
           const uint32_t c = lcnt[ls];
           const uint32_t nent = c & 0x7fffffffu;
           const uint32_t land = smem0 + land_off + ls * (kLandCap * 8);
-          const uint32_t j = 4 * ct;
+          const uint32_t j = EPT * ct;
           if (j < nent) {
-            const uint4 e01 = ld_shared_v4(land + 8 * j), e23 = ld_shared_v4(land + 8 * j + 16);
-            const uint32_t ex[4] = {e01.x, e01.z, e23.x, e23.z}, ey[4] = {e01.y, e01.w, e23.y, e23.w};
-            if (total + j < (uint32_t)kUndoCap)
-              st_shared_v2(undo + 2 * (total + j), (ex[0] & 0xFFFFu) | (ex[1] << 16), (ex[2] & 0xFFFFu) | (ex[3] << 16));
+            uint32_t ex[EPT], ey[EPT];
+            if (EPT == 4) {
+              const uint4 e01 = ld_shared_v4(land + 8 * j), e23 = ld_shared_v4(land + 8 * j + 16);
+              ex[0] = e01.x; ey[0] = e01.y; ex[1] = e01.z; ey[1] = e01.w;
+              ex[EPT - 2] = e23.x; ey[EPT - 2] = e23.y; ex[EPT - 1] = e23.z; ey[EPT - 1] = e23.w;
+            } else {
+              const uint4 e01 = ld_shared_v4(land + 8 * j);
+              ex[0] = e01.x; ey[0] = e01.y; ex[1] = e01.z; ey[1] = e01.w;
+            }
+            if (total + j < (uint32_t)kUndoCap) {
+              if (EPT == 4) st_shared_v2(undo + 2 * (total + j), (ex[0] & 0xFFFFu) | (ex[1] << 16), (ex[EPT - 2] & 0xFFFFu) | (ex[EPT - 1] << 16));
+              else st_shared_u32(undo + 2 * (total + j), (ex[0] & 0xFFFFu) | (ex[1] << 16));
+            }
 #pragma unroll
-            for (int e = 0; e < 4; ++e) {
+            for (int e = 0; e < EPT; ++e) {
               const uint32_t pos = ex[e] & 0xFFFFu;
               if (pos != kPosSkip) {
                 const uint32_t ad = abase + 2 * pos;
@@ -251,33 +278,38 @@ __global__ void __launch_bounds__(384, 1) sparse_ts_kernel(const __grid_constant
           if (++ls == n_ls) { ls = 0; pl ^= 1u; }
           if (c & 0x80000000u) break;
         }
-        asm volatile("bar.sync 1, 128;" ::: "memory");  // the tile is complete
-        // ---- 2. my row of every half and plane: 8 x 16 bytes, chunk j of row r sits at (j ^ (r & 7)) in the swizzled layout
-        uint32_t r[MH * P * 32];
-#pragma unroll
-        for (int h = 0; h < MH; ++h) {
-          const int row = h * 128 + ct;
+        conv_bar<kConv>();                              // the tile is complete
+        // ---- 2. my row of every plane: 8 x 16 bytes, chunk j of row r sits at (j ^ (r & 7)) in the swizzled layout
+        uint32_t r[P * 32];
+        {
+          const int row = hh * 128 + rr;
           const uint32_t rbase = abase + (uint32_t)((row >> 3) << 10) + (uint32_t)((row & 7) << 7);
 #pragma unroll
           for (int p = 0; p < P; ++p) {
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
               const uint4 v = ld_shared_v4(rbase + p * pb + (uint32_t)((j ^ (row & 7)) << 4));
-              uint32_t* d = r + (h * P + p) * 32 + 4 * j;
+              uint32_t* d = r + p * 32 + 4 * j;
               d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
             }
           }
         }
-        asm volatile("bar.sync 1, 128;" ::: "memory");  // every row has been read: the zeros can come back
+        conv_bar<kConv>();                              // every row has been read: the zeros can come back
         // ---- 3. restore the zeros (the other staging tile takes the next k block meanwhile)
         if (total > (uint32_t)kUndoCap) {
-          for (uint32_t i = ct; i < (buf_bytes >> 4); i += 128) st_shared_zero16(abase + (i << 4));
+          for (uint32_t i = ct; i < (buf_bytes >> 4); i += kConv) st_shared_zero16(abase + (i << 4));
         } else {
-          for (uint32_t i = 4 * ct; i < total; i += 512) {
-            const uint2 pp = ld_shared_v2(undo + 2 * i);
-            const uint32_t ps[4] = {pp.x & 0xFFFFu, pp.x >> 16, pp.y & 0xFFFFu, pp.y >> 16};
+          for (uint32_t i = EPT * ct; i < total; i += 512) {
+            uint32_t ps[EPT];
+            if (EPT == 4) {
+              const uint2 pp = ld_shared_v2(undo + 2 * i);
+              ps[0] = pp.x & 0xFFFFu; ps[1] = pp.x >> 16; ps[EPT - 2] = pp.y & 0xFFFFu; ps[EPT - 1] = pp.y >> 16;
+            } else {
+              const uint32_t pp = ld_shared_u32(undo + 2 * i);
+              ps[0] = pp & 0xFFFFu; ps[1] = pp >> 16;
+            }
 #pragma unroll
-            for (int e = 0; e < 4; ++e) {
+            for (int e = 0; e < EPT; ++e) {
               if (ps[e] != kPosSkip) {
                 const uint32_t ad = abase + 2 * ps[e];
                 st_shared_u16(ad, 0u);
@@ -287,16 +319,18 @@ __global__ void __launch_bounds__(384, 1) sparse_ts_kernel(const __grid_constant
             }
           }
         }
-        // ---- 4. my rows into the TMEM copy of A (lane = row, column c = k 2c and 2c + 1)
-        mbar_wait(bar_taempty + 8 * ta, pta ^ 1u);      // the MMAs that read this TMEM stage have retired
+        // ---- 4. my row into this half's TMEM slot (lane = row, column c = k 2c and 2c + 1)
+        const int ta = (int)(it % n_ta);
+        const uint32_t pta = (uint32_t)((it / n_ta) & 1);
+        mbar_wait(bar_taempty + 8 * ta, pta ^ 1u);      // the MMAs that read this TMEM slot have retired
         tc_fence_after();
-        const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + a_col0 + (uint32_t)(ta * kStageCols);
+        const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + a_col0 + (uint32_t)(ta * kSlotCols);
 #pragma unroll
-        for (int hp = 0; hp < MH * P; ++hp) tmem_st32(tbase + hp * 32, r + hp * 32);
+        for (int p = 0; p < P; ++p) tmem_st32(tbase + p * 32, r + p * 32);
         tmem_st_wait();
         tc_fence_before();
         mbar_arrive(bar_tafull + 8 * ta);
-        if (++ta == n_ta) { ta = 0; pta ^= 1u; }
+        it += MH;
         buf ^= 1;
       }
     }
@@ -330,7 +364,7 @@ static int launch_ts(cudaStream_t s, const CUtensorMap& mX, const SparseTsArgs& 
     N2V2R_CUDA(cudaFuncSetAttribute(sparse_ts_kernel<MH, P>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024 - 1024)));
     attr_set = true;
   }
-  sparse_ts_kernel<MH, P><<<grid, 384, smem, s>>>(mX, a);
+  sparse_ts_kernel<MH, P><<<grid, 256 + 128 * MH, smem, s>>>(mX, a);
   N2V2R_CHECK_LAUNCH();
   return N2V2R_OK;
 }
@@ -356,10 +390,9 @@ int stream_apply_tiles_ts(cudaStream_t s, const StreamPlan& plan, const uint32_t
   }
   a.n_splits = (a.n_kb + a.kb_per_split - 1) / a.kb_per_split;
   N2V2R_REQUIRE(a.n_splits <= plan.n_splits, "compressed tiles: K split exceeds the workspace plan");
-  const int stage_cols = mh * n_planes * 32;
-  a.ta_stages = (512 - mh * 3 * plan.l) / stage_cols;
-  if (a.ta_stages > 4) a.ta_stages = 4;
-  N2V2R_REQUIRE(a.ta_stages >= 1, "compressed tiles (A in TMEM): accumulators and one A stage do not fit in tensor memory (l=%d)", plan.l);
+  a.ta_slots = (512 - mh * 3 * plan.l) / (n_planes * 32);
+  if (a.ta_slots > 4) a.ta_slots = 4;
+  N2V2R_REQUIRE(a.ta_slots >= mh, "compressed tiles (A in TMEM): accumulators and the A slots do not fit in tensor memory (l=%d)", plan.l);
   a.a_plane_bytes = 16384u * mh;
   a.a_buf_bytes = a.a_plane_bytes * n_planes;
   a.x_bytes = 3u * plan.l * 128u;
