@@ -70,7 +70,7 @@ def parse_args():
     ap.add_argument("--block-width", type=int, default=48, help="solver block width l (default = device.default_block_width(24, n))")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer end-to-end leg (development only)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (development only)")
-    ap.add_argument("--layer-storage", default="auto", choices=["auto", "planes", "tiles", "e4m3"],
+    ap.add_argument("--layer-storage", default="auto", choices=["auto", "planes", "tiles", "e4m3", "rows"],
                     help="how preprocessed layers are held in HBM (device.make_layer): dense bf16 planes, or compressed tiles "
                          "expanded in shared memory for sparse layers; auto = the product default")
     ap.add_argument("--no-cross-check", action="store_true",
@@ -387,6 +387,8 @@ class Env:
         self.hbm_peak, self.hbm_src = (float(peaks["hbm_gbs"]), "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
         key = "bf16_tflops_sustained" if "bf16_tflops_sustained" in peaks else "bf16_tflops"
         self.tc_peak, self.tc_src = (float(peaks[key]), f"measured ({key})") if key in peaks else (1394.0, "fallback")
+        self.sm_count = torch.cuda.get_device_properties(self.dev).multi_processor_count
+        self.sm_max_mhz = 1965.0           # clocks.max.sm of this pool's B200s (B200_PROFILING.md); the shared-memory peak is per clock
 
     def barrier(self):
         if self.world > 1:
@@ -755,7 +757,34 @@ def stream_roofline(env, infos, ms_step, steps, n, n_planes, l, workload, layers
               "share_of_step": mma_ms / max(ms_step * steps, 1e-9),
               "streaming_products_share_of_step": stream_ms / max(ms_step * steps, 1e-9)}
     tiles = bool(layers) and layers[0].storage == "tiles"
-    if tiles:
+    if bool(layers) and layers[0].storage == "rows":
+        # row lists (rows_product_kernel): HBM carries the lists once (8 bytes per non-zero + the u16 row headers) and the skinny
+        # operand / result; every CTA also reads the whole operand through L2 (panel by panel) and every entry gathers l x 4 bytes
+        # of it from shared memory -- that gather, at 128 B/clk/SM, is what bounds the launch, so it is reported beside the HBM line
+        L = layers[0]
+        list_bytes = float(np.mean([x.n_units * 16 + x.tile_ptr.numel() * 4 for x in layers]))
+        nnz = float(np.mean([x.n_entries for x in layers]))
+        alg_bytes = list_bytes + 4.0 * l * 2.0 * n
+        achieved = alg_bytes / avg_s / 1e9 if mma_n else 0.0
+        n_blocks = -(-n // L.tile_rows)
+        sms, clk_hz = env.sm_count, env.sm_max_mhz * 1e6
+        gather = nnz * l * 4.0
+        roof = {"bound": "hbm", "achieved": achieved, "peak": env.hbm_peak, "unit": "GB/s", "frac": achieved / env.hbm_peak,
+                "traffic": None, "kernel": "rows_product_kernel", "peak_source": env.hbm_src,
+                "algorithmic_bytes_per_launch": alg_bytes, "nonzeros_per_launch": nnz,
+                "fp32_flop_per_launch": 2.0 * nnz * l,
+                "shared_memory_gather": {"bytes_per_launch": gather, "achieved_bytes_per_clk_per_sm": (gather / avg_s / clk_hz / sms) if mma_n else 0.0,
+                                         "peak_bytes_per_clk_per_sm": 128.0,
+                                         "frac": (gather / avg_s / clk_hz / sms / 128.0) if mma_n else 0.0,
+                                         "clock_mhz_assumed": env.sm_max_mhz},
+                "l2_operand_bytes_per_launch": float(n_blocks) * n * l * 4.0,
+                "dense_planes_bytes_per_launch": float(n) * n * 2.0 * 2 + 8.0 * l * n,
+                "note": "a different algorithm from the dense-plane stream and from the compressed tiles (profiles/: both lines are kept "
+                        "beside it): the layer crosses HBM as row lists of its non-zeros (exact fp32 values) and is multiplied entry by "
+                        "entry on the FMA pipes; the launch is bound by the shared-memory gather of the operand rows (l x 4 bytes per "
+                        "8-byte entry), not by HBM, so the HBM fraction is low by construction"}
+        key = f"{workload}_rows_bytes_per_launch"
+    elif tiles:
         L = layers[0]
         terms = {1: 3, 2: 5, 3: 6}[n_planes]
         rows_pad = -(-n // L.tile_rows) * L.tile_rows

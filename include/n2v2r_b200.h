@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define N2V2R_ABI_VERSION 2
+#define N2V2R_ABI_VERSION 3
 
 typedef enum {
   N2V2R_OK = 0,
@@ -48,9 +48,10 @@ typedef enum { N2V2R_F32 = 0, N2V2R_F64 = 1 } n2v2r_dtype_t;
 typedef enum { N2V2R_EUCLIDEAN = 0, N2V2R_COSINE = 1, N2V2R_CORRELATION = 2 } n2v2r_metric_t;
 typedef enum { N2V2R_SEQUENTIAL = 0, N2V2R_ONE_VS_BEFORE = 1, N2V2R_ONE_VS_REST = 2 } n2v2r_strategy_t;
 typedef enum { N2V2R_ALGO_TCGEN05 = 0, N2V2R_ALGO_SIMT = 1 } n2v2r_algo_t;
-/* how a layer is held in HBM: dense bf16 planes; compressed tiles (sparse layers, expanded in shared memory); or ONE e4m3
- * plane of 1 byte per entry (binarised layers and any layer whose entries e4m3 represents exactly) */
-typedef enum { N2V2R_STORE_PLANES = 0, N2V2R_STORE_TILES = 1, N2V2R_STORE_E4M3 = 2 } n2v2r_storage_t;
+/* how a layer is held in HBM: dense bf16 planes; compressed tiles (sparse layers, expanded in shared memory for the tensor
+ * cores); ONE e4m3 plane of 1 byte per entry (binarised layers and any layer whose entries e4m3 represents exactly); or row
+ * lists (sparse layers, exact fp32 values, multiplied entry by entry on the FMA pipes: "K1d row lists" below) */
+typedef enum { N2V2R_STORE_PLANES = 0, N2V2R_STORE_TILES = 1, N2V2R_STORE_E4M3 = 2, N2V2R_STORE_ROWS = 3 } n2v2r_storage_t;
 
 int n2v2r_abi_version(void);
 const char* n2v2r_last_error(void);
@@ -159,6 +160,24 @@ int n2v2r_project(void* stream, const void* d_W, int dtype, int64_t rows, int64_
                   int on_rows, float* d_out, int64_t ld_out, void* d_ws, size_t ws_bytes);
 
 /* ------------------------------------------------------------------------------------
+ * K1d  row lists: the storage of a SPARSE layer for the FMA-pipe product (k3_rows.cu).  The rows are cut into blocks of
+ * rows_per_block (one CTA each; <= 528), the columns into panels of panel_cols (multiple of 32).  The non-zeros of
+ * (block b, panel p) form one list: a u16 header of rows_per_block + 1 entry offsets (padded to 16 bytes) followed by the
+ * 8-byte entries {u32 column inside the panel, fp32 value} sorted by row then column, padded to 16 bytes.
+ * d_list_ptr[b n_panels + p] is the offset of the list in 16-byte units, d_list_ptr[n_blocks n_panels] the total.
+ * Build: count (per-row counts, list offsets; returns the total size in 16-byte units, the longest list in bytes and the
+ * number of non-zeros; synchronises) -> allocate -> fill.  The lists of A^T are built from a transposed copy of the input.
+ * ---------------------------------------------------------------------------------- */
+size_t n2v2r_rows_counts_bytes(int64_t n, int rows_per_block, int panel_cols);
+int n2v2r_rows_count(void* stream, const float* d_in, int64_t n, int64_t ld, int rows_per_block, int panel_cols,
+                     void* d_counts, uint32_t* d_list_ptr, int64_t* h_units, int32_t* h_max_list_bytes, int64_t* h_nnz);
+int n2v2r_rows_fill(void* stream, const float* d_in, int64_t n, int64_t ld, int rows_per_block, int panel_cols,
+                    const void* d_counts, const uint32_t* d_list_ptr, void* d_lists);
+/* d_out (n x ld_out fp32, zero-filled by the caller) = the matrix the lists hold */
+int n2v2r_rows_to_dense(void* stream, const uint32_t* d_list_ptr, const void* d_lists, int64_t n, int rows_per_block,
+                        int panel_cols, float* d_out, int64_t ld_out);
+
+/* ------------------------------------------------------------------------------------
  * K3-K8  UASE: truncated SVD of the unfolded matrix [A_1 | ... | A_T] and the per-layer
  * right embeddings V_t * S^(1/2).  Replaces spectral_embedding.UASE as called at
  * model.py:54-55 (scipy svds / ARPACK underneath).
@@ -181,12 +200,15 @@ typedef struct {
   const uint32_t* d_tile_ptr_t;  /* tiles of A^T, or NULL when the layer is symmetric    */
   const void* d_entries_t;
   int64_t n_entries, n_entries_t;
-  int32_t tile_rows;             /* 128 or 256                                           */
-  int32_t reserved;
+  int32_t tile_rows;             /* TILES: 128 or 256; ROWS: rows per block                */
+  int32_t panel_cols;            /* ROWS: columns per panel (ABI 2: reserved)              */
   /* ROW SLAB of a layer (bf16 planes only; sharding of ONE layer over several processes when there are fewer layers
    * than GPUs): rows > 0 means this process holds rows [row_offset, row_offset + rows) of the n x n layer:
    * d_planes = the slab (rows x ld), d_planes_t = its transpose (n x ld_t, ld_t a multiple of 64 >= rows; required). */
   int64_t row_offset, rows, ld_t;
+  /* N2V2R_STORE_ROWS (ABI 3): d_tile_ptr / d_tile_ptr_t = the list offsets (16-byte units), d_entries / d_entries_t = the
+   * lists, n_entries / n_entries_t = non-zeros; the longest list of A and of A^T in bytes (n2v2r_rows_count) */
+  int32_t list_cap, list_cap_t;
 } n2v2r_layer_t;
 
 typedef struct {

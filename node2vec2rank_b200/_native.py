@@ -27,7 +27,7 @@ class NativeError(RuntimeError):
         self.status = status
 
 
-STORE_PLANES, STORE_TILES, STORE_E4M3 = 0, 1, 2
+STORE_PLANES, STORE_TILES, STORE_E4M3, STORE_ROWS = 0, 1, 2, 3
 MAX_CHECK = 32
 
 
@@ -35,8 +35,8 @@ class Layer(C.Structure):
     _fields_ = [("d_planes", C.c_void_p), ("d_planes_t", C.c_void_p), ("n_planes", C.c_int32),
                 ("storage", C.c_int32), ("ld", C.c_int64),
                 ("d_tile_ptr", C.c_void_p), ("d_entries", C.c_void_p), ("d_tile_ptr_t", C.c_void_p), ("d_entries_t", C.c_void_p),
-                ("n_entries", C.c_int64), ("n_entries_t", C.c_int64), ("tile_rows", C.c_int32), ("reserved", C.c_int32),
-                ("row_offset", C.c_int64), ("rows", C.c_int64), ("ld_t", C.c_int64)]
+                ("n_entries", C.c_int64), ("n_entries_t", C.c_int64), ("tile_rows", C.c_int32), ("panel_cols", C.c_int32),
+                ("row_offset", C.c_int64), ("rows", C.c_int64), ("ld_t", C.c_int64), ("list_cap", C.c_int32), ("list_cap_t", C.c_int32)]
 
 
 class UaseParams(C.Structure):
@@ -79,6 +79,10 @@ SIGNATURES = {
     "n2v2r_tiles_scan": (_i, [_vp, _vp, _i64, _i, _vp, C.POINTER(_i64)]),
     "n2v2r_tiles_fill": (_i, [_vp, _vp, _i64, _i64, _i, _i, _vp, _vp]),
     "n2v2r_tiles_to_dense": (_i, [_vp, _vp, _vp, _i64, _i, _vp, _i64]),
+    "n2v2r_rows_counts_bytes": (_sz, [_i64, _i, _i]),
+    "n2v2r_rows_count": (_i, [_vp, _vp, _i64, _i64, _i, _i, _vp, _vp, C.POINTER(C.c_int64), C.POINTER(C.c_int32), C.POINTER(C.c_int64)]),
+    "n2v2r_rows_fill": (_i, [_vp, _vp, _i64, _i64, _i, _i, _vp, _vp, _vp]),
+    "n2v2r_rows_to_dense": (_i, [_vp, _vp, _vp, _i64, _i, _i, _vp, _i64]),
     "n2v2r_project_workspace_bytes": (_sz, [_i64, _i64, _i]),
     "n2v2r_project": (_i, [_vp, _vp, _i, _i64, _i64, _i64, _i, _vp, _i64, _vp, _sz]),
     "n2v2r_uase_workspace_bytes": (_sz, [C.POINTER(UaseParams)]),
@@ -121,7 +125,7 @@ def load():
             fn = getattr(lib, name)            # AttributeError if the symbol is not exported
             fn.restype = res
             fn.argtypes = args
-        if lib.n2v2r_abi_version() != 2:
+        if lib.n2v2r_abi_version() != 3:
             raise ImportError("libn2v2r_b200.so ABI version mismatch")
         _lib = lib
     return _lib

@@ -19,7 +19,7 @@ PKG = os.path.dirname(HERE)
 ROOT = os.path.dirname(PKG)
 OUT = os.path.join(PKG, "libn2v2r_b200.so")
 OBJ = os.path.join(ROOT, "build", "obj")
-SOURCES = ["api.cu", "batch.cu", "comm.cu", "k0_pack.cu", "k1_preprocess.cu", "k3_stream.cu", "k3_tcgen05.cu", "k3_sparse.cu", "k3_sparse_ts.cu", "k3_fp8.cu", "k5_orth.cu", "k9_rank.cu", "uase_solver.cu"]
+SOURCES = ["api.cu", "batch.cu", "comm.cu", "k0_pack.cu", "k1_preprocess.cu", "k3_stream.cu", "k3_tcgen05.cu", "k3_sparse.cu", "k3_sparse_ts.cu", "k3_rows.cu", "k3_fp8.cu", "k5_orth.cu", "k9_rank.cu", "uase_solver.cu"]
 HOST_SOURCES = ["host_pack.cpp"]          # plain C++ (g++): host-side packing for the sparse PCIe transfer
 HOST_FLAGS = ["-O3", "-std=c++17", "-fPIC", "-pthread", "-fvisibility=default"]
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",

@@ -7,8 +7,9 @@
 // swizzled layout), writes it into tensor memory with tcgen05.st (lane = row, one 32-bit column = two consecutive k) and
 // restores the zeros at once; the MMAs take A from TMEM and only the split operand from shared memory.  The shared-memory
 // tile is free again as soon as it has been read, so what rings is the TMEM copy of A: slots of ONE 128-row half each (P x 32
-// columns) next to the accumulators, filled by the converter group of that half (128 threads per half: warps 8-11 own the rows
-// of half 0, warps 12-15 those of half 1) and released half by half as the MMAs retire.
+// columns) next to the accumulators, released half by half as the MMAs retire.  The chain scatter -> barrier -> read back ->
+// tcgen05.st -> barrier -> undo of one k block is latency, not bandwidth, so TWO converter teams of 128 threads (warps 8-11 and
+// 12-15) work on alternate k blocks, each with its own staging tile, undo list and ring of landing buffers.
 // Same entry format, same K split and MMA order as k3_sparse.cu: the product has the same bits.
 #include "sparse_common.cuh"
 #include <algorithm>
@@ -33,11 +34,7 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t* v) {
         "r"(v[30]), "r"(v[31])
       : "memory");
 }
-template <int N>
-__device__ __forceinline__ void conv_bar() {
-  if (N == 128) asm volatile("bar.sync 1, 128;" ::: "memory");
-  else asm volatile("bar.sync 1, 256;" ::: "memory");
-}
+__device__ __forceinline__ void team_bar(int team) { asm volatile("bar.sync %0, 128;" ::"r"(team + 1) : "memory"); }
 __device__ __forceinline__ void st_shared_u32(uint32_t addr, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory"); }
 __device__ __forceinline__ uint32_t ld_shared_u32(uint32_t addr) {
   uint32_t v;
@@ -47,7 +44,7 @@ __device__ __forceinline__ uint32_t ld_shared_u32(uint32_t addr) {
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
 struct SparseTsArgs {
-  int l, x_stages, l_slots, ta_slots;       // ta_slots: TMEM A slots of one 128-row half each
+  int l, x_stages, l_slots, ta_slots;       // l_slots: landing buffers PER TEAM; ta_slots: TMEM A slots of one 128-row half each
   int n_tiles, n_splits, kb_per_split, n_kb;
   int64_t rows_valid, out_ld, split_stride;
   uint32_t a_plane_bytes, a_buf_bytes, x_bytes;
@@ -59,7 +56,7 @@ struct SparseTsArgs {
 
 // MH = 128-row halves per tile (tile_rows / 128), P = bf16 plane terms.  Warp roles as in sparse_mma_kernel.
 template <int MH, int P>
-__global__ void __launch_bounds__(256 + 128 * MH, 1) sparse_ts_kernel(const __grid_constant__ CUtensorMap mapX, const SparseTsArgs a) {
+__global__ void __launch_bounds__(512, 1) sparse_ts_kernel(const __grid_constant__ CUtensorMap mapX, const SparseTsArgs a) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bars[40];
   __shared__ uint32_t tmem_base_smem;
@@ -74,13 +71,13 @@ __global__ void __launch_bounds__(256 + 128 * MH, 1) sparse_ts_kernel(const __gr
   const int n_units = a.n_tiles * a.n_splits;
   const int nacc = 3 * a.l;
   constexpr int kSlotCols = P * 32;                      // TMEM columns of one A slot: one half, per plane 64 k = 32 columns
-  constexpr int kConv = 128 * MH;                        // converter threads
+  constexpr int kTeam = 128;                             // threads of one converter team
   const uint32_t a_col0 = (uint32_t)(MH * nacc);         // the A ring follows the accumulators
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < a.x_stages; ++i) { mbar_init(bar_xfull + 8 * i, 1); mbar_init(bar_xempty + 8 * i, 1); }
     for (int i = 0; i < a.ta_slots; ++i) { mbar_init(bar_tafull + 8 * i, 128); mbar_init(bar_taempty + 8 * i, 1); }
-    for (int i = 0; i < a.l_slots; ++i) { mbar_init(bar_lfull + 8 * i, 1); mbar_init(bar_lempty + 8 * i, kConv); }
+    for (int i = 0; i < 2 * a.l_slots; ++i) { mbar_init(bar_lfull + 8 * i, 1); mbar_init(bar_lempty + 8 * i, kTeam); }
     mbar_init(bar_tfull, 1);
     mbar_init(bar_tempty, 4);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -152,8 +149,9 @@ __global__ void __launch_bounds__(256 + 128 * MH, 1) sparse_ts_kernel(const __gr
       uphase ^= 1u;
     }
   } else if (warp == 2) {
-    // ===== producer of the entry lists =====
-    int ls = 0; uint32_t pl = 0;
+    // ===== producer of the entry lists: k block i of this CTA goes to the landing ring of team i & 1 =====
+    int ls0 = 0, ls1 = 0; uint32_t pl0 = 0, pl1 = 0;
+    int tm = 0;                                          // team of the next k block
     for (int u = blockIdx.x; u < n_units; u += gridDim.x) {
       const int split = u / a.n_tiles, tile = u - split * a.n_tiles;
       const int kb0 = split * a.kb_per_split, kb1 = min(a.n_kb, kb0 + a.kb_per_split);
@@ -169,20 +167,24 @@ __global__ void __launch_bounds__(256 + 128 * MH, 1) sparse_ts_kernel(const __gr
           const uint32_t p1 = __shfl_sync(0xffffffffu, v1, i);
           if (lane == 0) {
             uint32_t left = p1 - p0;
+            int lsv = tm ? ls1 : ls0; uint32_t plv = tm ? pl1 : pl0;
             do {
               const uint32_t c = left < (uint32_t)kLandCap ? left : (uint32_t)kLandCap;
-              mbar_wait(bar_lempty + 8 * ls, pl ^ 1u);
-              lcnt[ls] = c | (left == c ? 0x80000000u : 0u);
+              const int slot = tm * a.l_slots + lsv;
+              mbar_wait(bar_lempty + 8 * slot, plv ^ 1u);
+              lcnt[slot] = c | (left == c ? 0x80000000u : 0u);
               if (c) {
-                mbar_expect_tx(bar_lfull + 8 * ls, c * 8u);
-                bulk_copy_g2s(smem0 + a.off_land + ls * (kLandCap * 8), a.entries + p0, c * 8u, bar_lfull + 8 * ls);
+                mbar_expect_tx(bar_lfull + 8 * slot, c * 8u);
+                bulk_copy_g2s(smem0 + a.off_land + slot * (kLandCap * 8), a.entries + p0, c * 8u, bar_lfull + 8 * slot);
               } else {
-                mbar_arrive(bar_lfull + 8 * ls);
+                mbar_arrive(bar_lfull + 8 * slot);
               }
               p0 += c; left -= c;
-              if (++ls == a.l_slots) { ls = 0; pl ^= 1u; }
+              if (++lsv == a.l_slots) { lsv = 0; plv ^= 1u; }
             } while (left);
+            if (tm) { ls1 = lsv; pl1 = plv; } else { ls0 = lsv; pl0 = plv; }
           }
+          tm ^= 1;
           __syncwarp();
         }
       }
@@ -224,46 +226,42 @@ __global__ void __launch_bounds__(256 + 128 * MH, 1) sparse_ts_kernel(const __gr
       uphase ^= 1u;
     }
   } else if (warp >= 8) {
-    // ===== converters: entry lists -> zeroed SWIZZLE_128B staging tile -> own row -> tensor memory =====
-    const int ct = threadIdx.x - 256;                  // 0 .. 128 MH - 1
-    const int hh = ct >> 7;                            // the 128-row half whose rows this thread's warp group owns
-    const int rr = ct & 127;                           // row inside the half = TMEM lane
+    // ===== converters: entry lists -> zeroed SWIZZLE_128B staging tile -> own rows -> tensor memory =====
+    const int ct = threadIdx.x - 256;                  // 0 .. 255
+    const int tm = ct >> 7;                            // team: takes the k blocks i of this CTA with (i & 1) == tm
+    const int rr = ct & 127;                           // row inside a half = TMEM lane
     const int q = warp & 3;                            // TMEM lane quarter of this warp
-    int ls = 0, buf = 0; uint32_t pl = 0;
-    long it = hh;                                      // running index of this group's (k block, half) items: it = i MH + hh
-    const uint32_t pb = a.a_plane_bytes, buf_bytes = a.a_buf_bytes, land_off = a.off_land, undo_off = a.off_undo;
+    int ls = 0; uint32_t pl = 0;
+    long ikb = 0;                                      // running k block index of this CTA
+    const uint32_t pb = a.a_plane_bytes, buf_bytes = a.a_buf_bytes;
+    const uint32_t abase = smem0 + tm * buf_bytes;
+    const uint32_t undo = smem0 + a.off_undo + tm * (kUndoCap * 2);
+    const uint32_t land0 = smem0 + a.off_land + tm * a.l_slots * (kLandCap * 8);
+    const uint32_t lfull0 = bar_lfull + 8 * tm * a.l_slots, lempty0 = bar_lempty + 8 * tm * a.l_slots;
+    const uint32_t* lc = lcnt + tm * a.l_slots;
     const int n_ls = a.l_slots, n_ta = a.ta_slots;
     for (int u = blockIdx.x; u < n_units; u += gridDim.x) {
       const int split = u / a.n_tiles;
       const int kb0 = split * a.kb_per_split, kb1 = min(a.n_kb, kb0 + a.kb_per_split);
-      for (int kb = kb0; kb < kb1; ++kb) {
-        const uint32_t abase = smem0 + buf * buf_bytes;
-        const uint32_t undo = smem0 + undo_off + buf * (kUndoCap * 2);
+      for (int kb = kb0; kb < kb1; ++kb, ++ikb) {
+        if ((int)(ikb & 1) != tm) continue;
         // ---- 1. scatter this k block's entries into the (zero) staging tile, remembering the positions
-        constexpr int EPT = 512 / kConv;               // entries per thread and chunk: 4 (128 converters) or 2 (256)
         uint32_t total = 0;
         while (true) {
-          mbar_wait(bar_lfull + 8 * ls, pl);
-          const uint32_t c = lcnt[ls];
+          mbar_wait(lfull0 + 8 * ls, pl);
+          const uint32_t c = lc[ls];
           const uint32_t nent = c & 0x7fffffffu;
-          const uint32_t land = smem0 + land_off + ls * (kLandCap * 8);
-          const uint32_t j = EPT * ct;
+          const uint32_t land = land0 + ls * (kLandCap * 8);
+          const uint32_t j = 4 * rr;
           if (j < nent) {
-            uint32_t ex[EPT], ey[EPT];
-            if (EPT == 4) {
-              const uint4 e01 = ld_shared_v4(land + 8 * j), e23 = ld_shared_v4(land + 8 * j + 16);
-              ex[0] = e01.x; ey[0] = e01.y; ex[1] = e01.z; ey[1] = e01.w;
-              ex[EPT - 2] = e23.x; ey[EPT - 2] = e23.y; ex[EPT - 1] = e23.z; ey[EPT - 1] = e23.w;
-            } else {
-              const uint4 e01 = ld_shared_v4(land + 8 * j);
-              ex[0] = e01.x; ey[0] = e01.y; ex[1] = e01.z; ey[1] = e01.w;
-            }
-            if (total + j < (uint32_t)kUndoCap) {
-              if (EPT == 4) st_shared_v2(undo + 2 * (total + j), (ex[0] & 0xFFFFu) | (ex[1] << 16), (ex[EPT - 2] & 0xFFFFu) | (ex[EPT - 1] << 16));
-              else st_shared_u32(undo + 2 * (total + j), (ex[0] & 0xFFFFu) | (ex[1] << 16));
-            }
+            uint32_t ex[4], ey[4];
+            const uint4 e01 = ld_shared_v4(land + 8 * j), e23 = ld_shared_v4(land + 8 * j + 16);
+            ex[0] = e01.x; ey[0] = e01.y; ex[1] = e01.z; ey[1] = e01.w;
+            ex[2] = e23.x; ey[2] = e23.y; ex[3] = e23.z; ey[3] = e23.w;
+            if (total + j < (uint32_t)kUndoCap)
+              st_shared_v2(undo + 2 * (total + j), (ex[0] & 0xFFFFu) | (ex[1] << 16), (ex[2] & 0xFFFFu) | (ex[3] << 16));
 #pragma unroll
-            for (int e = 0; e < EPT; ++e) {
+            for (int e = 0; e < 4; ++e) {
               const uint32_t pos = ex[e] & 0xFFFFu;
               if (pos != kPosSkip) {
                 const uint32_t ad = abase + 2 * pos;
@@ -273,16 +271,18 @@ __global__ void __launch_bounds__(256 + 128 * MH, 1) sparse_ts_kernel(const __gr
               }
             }
           }
-          mbar_arrive(bar_lempty + 8 * ls);
+          mbar_arrive(lempty0 + 8 * ls);
           total += nent;
           if (++ls == n_ls) { ls = 0; pl ^= 1u; }
           if (c & 0x80000000u) break;
         }
-        conv_bar<kConv>();                              // the tile is complete
-        // ---- 2. my row of every plane: 8 x 16 bytes, chunk j of row r sits at (j ^ (r & 7)) in the swizzled layout
-        uint32_t r[P * 32];
-        {
-          const int row = hh * 128 + rr;
+        team_bar(tm);                                   // the tile is complete
+        // ---- 2. my row of every half and plane (8 x 16 bytes per plane; chunk j of row r sits at (j ^ (r & 7)) in the swizzled
+        //         layout) into the TMEM slot of that half: lane = row, column c = k 2c and 2c + 1
+#pragma unroll
+        for (int h = 0; h < MH; ++h) {
+          uint32_t r[P * 32];
+          const int row = h * 128 + rr;
           const uint32_t rbase = abase + (uint32_t)((row >> 3) << 10) + (uint32_t)((row & 7) << 7);
 #pragma unroll
           for (int p = 0; p < P; ++p) {
@@ -293,23 +293,28 @@ __global__ void __launch_bounds__(256 + 128 * MH, 1) sparse_ts_kernel(const __gr
               d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
             }
           }
-        }
-        conv_bar<kConv>();                              // every row has been read: the zeros can come back
-        // ---- 3. restore the zeros (the other staging tile takes the next k block meanwhile)
-        if (total > (uint32_t)kUndoCap) {
-          for (uint32_t i = ct; i < (buf_bytes >> 4); i += kConv) st_shared_zero16(abase + (i << 4));
-        } else {
-          for (uint32_t i = EPT * ct; i < total; i += 512) {
-            uint32_t ps[EPT];
-            if (EPT == 4) {
-              const uint2 pp = ld_shared_v2(undo + 2 * i);
-              ps[0] = pp.x & 0xFFFFu; ps[1] = pp.x >> 16; ps[EPT - 2] = pp.y & 0xFFFFu; ps[EPT - 1] = pp.y >> 16;
-            } else {
-              const uint32_t pp = ld_shared_u32(undo + 2 * i);
-              ps[0] = pp & 0xFFFFu; ps[1] = pp >> 16;
-            }
+          const long it = ikb * MH + h;
+          const int ta = (int)(it % n_ta);
+          const uint32_t pta = (uint32_t)((it / n_ta) & 1);
+          mbar_wait(bar_taempty + 8 * ta, pta ^ 1u);    // the MMAs that read this TMEM slot have retired
+          tc_fence_after();
+          const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + a_col0 + (uint32_t)(ta * kSlotCols);
 #pragma unroll
-            for (int e = 0; e < EPT; ++e) {
+          for (int p = 0; p < P; ++p) tmem_st32(tbase + p * 32, r + p * 32);
+          tmem_st_wait();
+          tc_fence_before();
+          mbar_arrive(bar_tafull + 8 * ta);
+        }
+        team_bar(tm);                                   // every row has been read: the zeros can come back
+        // ---- 3. restore the zeros
+        if (total > (uint32_t)kUndoCap) {
+          for (uint32_t i = rr; i < (buf_bytes >> 4); i += kTeam) st_shared_zero16(abase + (i << 4));
+        } else {
+          for (uint32_t i = 4 * rr; i < total; i += 512) {
+            const uint2 pp = ld_shared_v2(undo + 2 * i);
+            const uint32_t ps[4] = {pp.x & 0xFFFFu, pp.x >> 16, pp.y & 0xFFFFu, pp.y >> 16};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
               if (ps[e] != kPosSkip) {
                 const uint32_t ad = abase + 2 * ps[e];
                 st_shared_u16(ad, 0u);
@@ -319,19 +324,6 @@ __global__ void __launch_bounds__(256 + 128 * MH, 1) sparse_ts_kernel(const __gr
             }
           }
         }
-        // ---- 4. my row into this half's TMEM slot (lane = row, column c = k 2c and 2c + 1)
-        const int ta = (int)(it % n_ta);
-        const uint32_t pta = (uint32_t)((it / n_ta) & 1);
-        mbar_wait(bar_taempty + 8 * ta, pta ^ 1u);      // the MMAs that read this TMEM slot have retired
-        tc_fence_after();
-        const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + a_col0 + (uint32_t)(ta * kSlotCols);
-#pragma unroll
-        for (int p = 0; p < P; ++p) tmem_st32(tbase + p * 32, r + p * 32);
-        tmem_st_wait();
-        tc_fence_before();
-        mbar_arrive(bar_tafull + 8 * ta);
-        it += MH;
-        buf ^= 1;
       }
     }
   }
@@ -364,7 +356,7 @@ static int launch_ts(cudaStream_t s, const CUtensorMap& mX, const SparseTsArgs& 
     N2V2R_CUDA(cudaFuncSetAttribute(sparse_ts_kernel<MH, P>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024 - 1024)));
     attr_set = true;
   }
-  sparse_ts_kernel<MH, P><<<grid, 256 + 128 * MH, smem, s>>>(mX, a);
+  sparse_ts_kernel<MH, P><<<grid, 512, smem, s>>>(mX, a);
   N2V2R_CHECK_LAUNCH();
   return N2V2R_OK;
 }
@@ -397,14 +389,14 @@ int stream_apply_tiles_ts(cudaStream_t s, const StreamPlan& plan, const uint32_t
   a.a_buf_bytes = a.a_plane_bytes * n_planes;
   a.x_bytes = 3u * plan.l * 128u;
   const uint32_t budget = 227u * 1024u - 1024u - 1024u;
-  a.l_slots = 8;
+  a.l_slots = 4;                                          // per team
   const uint32_t fixed = 2u * a.a_buf_bytes + 2u * (uint32_t)(kUndoCap * 2);
-  while (a.l_slots > 3 && fixed + a.l_slots * (uint32_t)(kLandCap * 8) + 2 * a.x_bytes > budget) --a.l_slots;
-  N2V2R_REQUIRE(fixed + a.l_slots * (uint32_t)(kLandCap * 8) + 2 * a.x_bytes <= budget, "compressed tiles (A in TMEM): stages do not fit in shared memory");
-  a.x_stages = (int)std::min<uint32_t>(8u, (budget - fixed - a.l_slots * (uint32_t)(kLandCap * 8)) / a.x_bytes);
+  while (a.l_slots > 2 && fixed + 2u * a.l_slots * (uint32_t)(kLandCap * 8) + 2 * a.x_bytes > budget) --a.l_slots;
+  N2V2R_REQUIRE(fixed + 2u * a.l_slots * (uint32_t)(kLandCap * 8) + 2 * a.x_bytes <= budget, "compressed tiles (A in TMEM): stages do not fit in shared memory");
+  a.x_stages = (int)std::min<uint32_t>(8u, (budget - fixed - 2u * a.l_slots * (uint32_t)(kLandCap * 8)) / a.x_bytes);
   a.off_x = 2u * a.a_buf_bytes;
   a.off_land = a.off_x + a.x_stages * a.x_bytes;
-  a.off_undo = a.off_land + a.l_slots * (uint32_t)(kLandCap * 8);
+  a.off_undo = a.off_land + 2u * a.l_slots * (uint32_t)(kLandCap * 8);
   const size_t smem = (size_t)a.off_undo + 2u * (kUndoCap * 2) + 1024;
   const int64_t rows_pad = round_up(plan.n, 256);
   a.rows_valid = rows_pad;

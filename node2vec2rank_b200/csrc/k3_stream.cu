@@ -19,6 +19,8 @@ int stream_apply_e4m3(cudaStream_t s, const StreamPlan& plan, const void* plane8
                       float* parts, float* out, int accumulate);                                        // k3_fp8.cu
 int stream_apply_tiles(cudaStream_t s, const StreamPlan& plan, const uint32_t* tile_ptr, const void* entries, int n_planes,
                        int tile_rows, const float* x, __nv_bfloat16* xs, float* parts, float* out, int accumulate);   // k3_sparse.cu
+int stream_apply_rows(cudaStream_t s, int64_t n, int l, const uint32_t* list_ptr, const void* lists, int rb, int W, int list_cap,
+                      const float* x, float* out, int accumulate);                                        // k3_rows.cu
 
 template <int LC>
 __global__ void __launch_bounds__(256) simt_apply_kernel(const __nv_bfloat16* __restrict__ planes, int n_planes, int64_t n,
@@ -123,6 +125,13 @@ int stream_apply(cudaStream_t s, const StreamPlan& plan, const n2v2r_layer_t& L,
       *bytes_moved += 8.0 * (double)((transpose && L.d_entries_t) ? L.n_entries_t : L.n_entries) +
                       4.0 * (double)((plan.n + L.tile_rows - 1) / L.tile_rows) * (double)(plan.n_pad / 64) + 4.0 * plan.l * 2.0 * (double)plan.n;
     return stream_apply_tiles(s, plan, tp, en, L.n_planes, L.tile_rows, x, xs, parts, out, accumulate);
+  }
+  if (L.storage == N2V2R_STORE_ROWS) {
+    const bool tr = transpose && L.d_tile_ptr_t;
+    if (bytes_moved)   // the lists once + list offsets + skinny operand read + skinny result written
+      *bytes_moved += 8.0 * (double)(tr ? L.n_entries_t : L.n_entries) + 4.0 * plan.l * 2.0 * (double)plan.n;
+    return stream_apply_rows(s, plan.n, plan.l, tr ? L.d_tile_ptr_t : L.d_tile_ptr, tr ? L.d_entries_t : L.d_entries, L.tile_rows,
+                             L.panel_cols, tr ? L.list_cap_t : L.list_cap, x, out, accumulate);
   }
   if (L.storage == N2V2R_STORE_E4M3) {
     const void* p8 = (transpose && L.d_planes_t) ? L.d_planes_t : L.d_planes;

@@ -22,8 +22,9 @@ def _dev():
 
 @dataclass
 class DeviceLayer:
-    """A preprocessed graph layer resident in HBM (see include/n2v2r_b200.h): dense bf16 planes, or -- for sparse
-    layers -- compressed tiles that the product kernel expands in shared memory (storage == "tiles")."""
+    """A preprocessed graph layer resident in HBM (see include/n2v2r_b200.h): dense bf16 planes, one e4m3 plane, or -- for
+    sparse layers -- row lists multiplied entry by entry in fp32 (storage == "rows") or compressed tiles that the product
+    kernel expands into dense bf16 tiles for the tensor cores (storage == "tiles")."""
     planes: torch.Tensor | None     # (P, n, ld) bf16, None for a tiles layer
     n: int
     ld: int
@@ -43,6 +44,11 @@ class DeviceLayer:
     row_offset: int = 0                    # row slab of a layer (make_slab_layer): rows [row_offset, row_offset + rows)
     rows: int = 0                          # 0 = the whole layer
     ld_t: int = 0
+    panel_cols: int = 0                    # row lists: columns per panel (tile_rows = rows per block)
+    list_cap: int = 0                      # row lists: longest list in bytes (A, A^T)
+    list_cap_t: int = 0
+    n_units: int = 0                       # row lists: size of the lists in 16-byte units (A, A^T)
+    n_units_t: int = 0
     dtype = np.float32
 
     def __post_init__(self):
@@ -53,6 +59,12 @@ class DeviceLayer:
         return (self.planes if self.planes is not None else self.tile_ptr).device
 
     def c_struct(self):
+        if self.storage == "rows":
+            return N.Layer(0, 0, self.n_planes, N.STORE_ROWS, self.ld,
+                           self.tile_ptr.data_ptr(), self.entries.data_ptr(),
+                           0 if self.tile_ptr_t is None else self.tile_ptr_t.data_ptr(),
+                           0 if self.entries_t is None else self.entries_t.data_ptr(),
+                           self.n_entries, self.n_entries_t, self.tile_rows, self.panel_cols, 0, 0, 0, self.list_cap, self.list_cap_t)
         if self.storage == "tiles":
             return N.Layer(0, 0, self.n_planes, N.STORE_TILES, self.ld,
                            self.tile_ptr.data_ptr(), self.entries.data_ptr(),
@@ -65,6 +77,11 @@ class DeviceLayer:
 
     def to_dense(self):
         """fp32 (n, n) device tensor reconstructed from the stored form (exact)."""
+        if self.storage == "rows":
+            out = torch.zeros((self.n, self.n), dtype=torch.float32, device=self.device)
+            N.check(N.load().n2v2r_rows_to_dense(N.stream_ptr(), N.ptr(self.tile_ptr), N.ptr(self.entries), self.n, self.tile_rows,
+                                                 self.panel_cols, N.ptr(out), self.n))
+            return out
         if self.storage == "tiles":
             out = torch.zeros((self.n, self.n), dtype=torch.float32, device=self.device)
             N.check(N.load().n2v2r_tiles_to_dense(N.stream_ptr(), N.ptr(self.tile_ptr), N.ptr(self.entries), self.n, self.tile_rows,
@@ -104,6 +121,8 @@ class DeviceLayer:
 
     @property
     def nbytes(self):
+        if self.storage == "rows":
+            return (self.n_units + self.n_units_t) * 16 + sum(t.numel() * 4 for t in (self.tile_ptr, self.tile_ptr_t) if t is not None)
         if self.storage == "tiles":
             return (self.n_entries + self.n_entries_t) * 8 + sum(t.numel() * 4 for t in (self.tile_ptr, self.tile_ptr_t) if t is not None)
         return self.planes.numel() * self.planes.element_size() * (2 if self.planes_t is not None else 1)
@@ -386,15 +405,94 @@ def make_tiles_layer(x32: torch.Tensor, colsum=None, max_density=None, tile_rows
                        n_entries=cnt, n_entries_t=cnt_t), P, bool(sym.value)
 
 
+ROWS_MAX_DENSITY = 0.045        # layers sparser than this are stored as row lists (storage="auto"): the fp32 FMA-pipe product costs
+                                # about 0.26 ms per percent of density at n = 50 000 against 0.96 ms for the tiles at any density
+ROWS_PANEL_COLS = 256           # columns per panel: the X panel (256 x l fp32) and the block's list make one stage in shared memory
+ROWS_MAX_LIST_BYTES = 36 * 1024  # longest (block, panel) list a layer may have: two stages must fit beside two X panels (l <= 80)
+ROWS_GROUPS = 176               # groups of 4 lanes per CTA of the product kernel (22 warps): rows per block <= 3 x this
+
+
+_SM_COUNT = {}
+
+
+def sm_count():
+    dev = torch.cuda.current_device()
+    if dev not in _SM_COUNT:
+        sms, cc, mem = C.c_int(0), C.c_int(0), C.c_size_t(0)
+        N.check(N.load().n2v2r_device_info(dev, C.byref(sms), C.byref(cc), C.byref(mem)))
+        _SM_COUNT[dev] = sms.value
+    return _SM_COUNT[dev]
+
+
+def rows_per_block(n):
+    """Rows per block of a row-list layer: one block per SM when the groups can own that many rows (<= 3 each), else the
+    smallest split into equal waves."""
+    sms = sm_count()
+    waves = 1
+    while (n + sms * waves - 1) // (sms * waves) > 3 * ROWS_GROUPS:
+        waves += 1
+    return max(1, (n + sms * waves - 1) // (sms * waves))
+
+
+def make_rows_layer(x32: torch.Tensor, colsum=None, max_density=None, rows_block=None, panel_cols=None, max_list_bytes=ROWS_MAX_LIST_BYTES):
+    """fp32 (n, n) device matrix -> DeviceLayer(storage="rows"), or None when the matrix is denser than `max_density` or one
+    of its (block, panel) lists is longer than `max_list_bytes` (a hub row block: the caller picks another storage)."""
+    lib = N.load()
+    n = x32.shape[0]
+    assert x32.dim() == 2 and x32.shape[0] == x32.shape[1] and x32.dtype == torch.float32, "layer must be a square float32 matrix"
+    if x32.stride(1) != 1:
+        x32 = x32.contiguous()
+    dev = x32.device
+    rb = int(rows_block) if rows_block else rows_per_block(n)
+    W = int(panel_cols) if panel_cols else ROWS_PANEL_COLS
+    n_lists = ((n + rb - 1) // rb) * ((n + W - 1) // W)
+
+    def build(src):
+        counts = torch.empty(lib.n2v2r_rows_counts_bytes(n, rb, W), dtype=torch.uint8, device=dev)
+        lp = torch.empty(n_lists + 1, dtype=torch.int32, device=dev)
+        units, cap, nnz = C.c_int64(0), C.c_int32(0), C.c_int64(0)
+        N.check(lib.n2v2r_rows_count(N.stream_ptr(), N.ptr(src), n, src.stride(0), rb, W, N.ptr(counts), N.ptr(lp),
+                                     C.byref(units), C.byref(cap), C.byref(nnz)))
+        if (max_density is not None and nnz.value > max_density * n * n) or (max_list_bytes and cap.value > max_list_bytes):
+            return None
+        lists = torch.empty((max(units.value, 1), 4), dtype=torch.int32, device=dev)
+        N.check(lib.n2v2r_rows_fill(N.stream_ptr(), N.ptr(src), n, src.stride(0), rb, W, N.ptr(counts), N.ptr(lp), N.ptr(lists)))
+        return lp, lists, units.value, cap.value, nnz.value
+
+    a = build(x32)
+    if a is None:
+        return None
+    sym = bool(torch.equal(x32, x32.t()))
+    at = None
+    if not sym:
+        at = build(x32.t().contiguous())
+        if at is None:
+            return None
+    if colsum is None:
+        colsum = x32.sum(dim=0, dtype=torch.float64)
+    return DeviceLayer(planes=None, n=n, ld=(n + 63) // 64 * 64, n_planes=3, symmetric=sym, colsum=colsum, storage="rows",
+                       tile_rows=rb, panel_cols=W, tile_ptr=a[0], entries=a[1], n_units=a[2], list_cap=a[3], n_entries=a[4],
+                       tile_ptr_t=None if at is None else at[0], entries_t=None if at is None else at[1],
+                       n_units_t=0 if at is None else at[2], list_cap_t=0 if at is None else at[3], n_entries_t=0 if at is None else at[4])
+
+
 def make_layer(x32: torch.Tensor, n_planes=None, colsum=None, check_symmetry=True, storage="auto"):
-    """fp32 (n, n) device matrix -> DeviceLayer: compressed tiles when the matrix is sparse (storage "auto": density <=
-    TILES_MAX_DENSITY and n >= TILES_MIN_N; "tiles": always), else bf16 planes + symmetry flag / transposed copy."""
+    """fp32 (n, n) device matrix -> DeviceLayer.  storage "auto" for n >= TILES_MIN_N: row lists when the density is <=
+    ROWS_MAX_DENSITY (and no list is too long for a stage), compressed tiles when it is <= TILES_MAX_DENSITY, one e4m3 plane
+    for binarised layers, else bf16 planes + symmetry flag / transposed copy.  "rows" / "tiles" / "planes" / "e4m3" force one."""
     n = x32.shape[0]
     assert x32.shape[0] == x32.shape[1], "layer must be square"
-    if storage not in ("auto", "planes", "tiles", "e4m3"):
+    if storage not in ("auto", "planes", "tiles", "e4m3", "rows"):
         raise ValueError(f"unknown layer storage {storage!r}")
     if storage == "e4m3":
         return make_layer(x32, n_planes=1, colsum=colsum, check_symmetry=check_symmetry, storage="planes").to_e4m3()
+    if storage == "rows" or (storage == "auto" and n >= TILES_MIN_N and n_planes is None):
+        layer = make_rows_layer(x32, colsum=colsum, max_density=None if storage == "rows" else ROWS_MAX_DENSITY,
+                                max_list_bytes=None if storage == "rows" else ROWS_MAX_LIST_BYTES)
+        if layer is not None:
+            return layer
+        if storage == "rows":
+            raise ValueError("layer cannot be stored as row lists")
     known_sym = None
     if storage == "tiles" or (storage == "auto" and n >= TILES_MIN_N and n_planes is None):
         layer, P, known_sym = make_tiles_layer(x32, colsum=colsum, max_density=None if storage == "tiles" else TILES_MAX_DENSITY)

@@ -24,7 +24,7 @@ def test_header_symbols_exported(lib):
         assert hasattr(lib, name), f"{name} declared in include/n2v2r_b200.h but not exported"
         assert name in _native.SIGNATURES, f"{name} has no ctypes signature"
     assert sorted(_native.SIGNATURES) == names
-    assert lib.n2v2r_abi_version() == 2
+    assert lib.n2v2r_abi_version() == 3
 
 
 def test_struct_layout_matches_header(lib, tmp_path):
