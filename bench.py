@@ -361,6 +361,14 @@ def run_reference_arm(args):
     return 0
 
 
+DTYPE_BY_STORAGE = {
+    "planes": "bf16 planes x3-split bf16 operand, fp32 accumulate (tcgen05), fp64 small dense",
+    "tiles": "bf16 planes x3-split bf16 operand, fp32 accumulate (tcgen05), fp64 small dense",
+    "e4m3": "e4m3 plane x 6-term scaled e4m3 operand, fp32 accumulate (tcgen05 kind::f8f6f4), fp64 small dense",
+    "rows": "f32 (exact fp32 layer values x fp32 operand, fp32 FMA accumulate on the CUDA cores), fp64 small dense",
+}
+
+
 # ---- B200 arm ------------------------------------------------------------------------------------
 class Env:
     """One process per GPU: device, rendezvous, barrier and max-over-ranks (torch.distributed over NCCL)."""
@@ -710,7 +718,7 @@ def run_b200_arm(args):
     line = {
         "metric": "UASE sweep+rank wall time", "value": ms_step / 1e3, "unit": "s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": False, "scaling": "strong", "vs_baseline": None,
-        "dtype": "bf16 planes x3-split bf16 operand, fp32 accumulate (tcgen05), fp64 small dense",
+        "dtype": DTYPE_BY_STORAGE.get(storage, DTYPE_BY_STORAGE["planes"]),
         "data": "synthetic",
         "config": {"workload": w["name"], "n": n, "layers": T, "communities": K, "block_width": l, "planes_per_layer": n_planes,
                    "layers_per_gpu": len(mine), "layer_storage": storage,
@@ -915,7 +923,7 @@ def run_b200_c5(args, w):
     line = {
         "metric": "UASE sweep+rank wall time", "value": ms_step / 1e3, "unit": "s", "n_gpus": env.world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": False, "scaling": "strong", "vs_baseline": None,
-        "dtype": "bf16 planes x3-split bf16 operand, fp32 accumulate (tcgen05), fp64 small dense", "data": "synthetic",
+        "dtype": DTYPE_BY_STORAGE.get(layer_storage, DTYPE_BY_STORAGE["planes"]), "data": "synthetic",
         "config": {"workload": w["name"], "n": n, "layers": T, "communities": K, "block_width": l, "seeds": len(seeds),
                    "seeds_per_gpu": len(mine), "planes_per_layer": 1, "layer_storage": layer_storage,
                    "l2_policy": "inputs larger than L2 (each layer pass streams 0.9-1.8 GB)",
