@@ -763,9 +763,9 @@ def preprocess_to_layer(x: torch.Tensor, threshold=None, top_percent_keep=100, b
     check_sym = not projected            # K2 mirrors the upper triangle: W^T W is exactly symmetric, and K1b is elementwise
     if storage == "e4m3" and not binarize:
         raise ValueError('layer storage "e4m3" needs binarised layers (values exactly representable in e4m3)')
-    if binarize and storage != "tiles":
+    if binarize and storage not in ("tiles", "rows"):
         P = 1
-    elif storage_planes and storage != "tiles":
+    elif storage_planes and storage not in ("tiles", "rows"):
         P = int(storage_planes)
     else:
         P = 0

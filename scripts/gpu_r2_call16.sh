@@ -1,0 +1,10 @@
+#!/bin/bash
+# Round-2 GPU call 16: whole suite + smoke + default bench with the row-list storage as the auto choice for sparse layers.
+set -u
+O=gpurun_out/r2c16; mkdir -p $O
+export N2V2R_TEST_LOG=$O/testlog
+timeout 2400 python -m pytest tests -m gpu -q > $O/pytest_gpu.log 2>&1; echo "gpu rc=$?" | tee $O/rc.txt
+timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > $O/smoke.log 2>&1; echo "smoke rc=$?" | tee -a $O/rc.txt
+timeout 900 python bench.py > $O/bench_n1_c3.json 2> $O/bench_n1_c3.err; echo "c3 rc=$?" | tee -a $O/rc.txt
+timeout 900 python bench.py --workload c3w24 --no-cpu --no-e2e > $O/bench_n1_c3w24_rows.json 2> $O/bench_n1_c3w24_rows.err; echo "c3w24 rows rc=$?" | tee -a $O/rc.txt
+grep -E "passed|failed" $O/pytest_gpu.log | tail -2; grep -E "^FAILED" $O/pytest_gpu.log; tail -1 $O/smoke.log; for f in $O/bench_*.json; do echo $f; cut -c1-200 $f; done

@@ -111,6 +111,7 @@ def test_tiles_solver_matches_planes_solver(gpu):
 def test_auto_storage_picks_tiles_for_large_sparse_layers(gpu, monkeypatch):
     from node2vec2rank_b200 import device as D
     monkeypatch.setattr(D, "TILES_MIN_N", 512)
+    monkeypatch.setattr(D, "ROWS_MAX_DENSITY", 0.0)          # the row lists would take this layer first (tests/test_gpu_rows.py)
     sparse = torch.from_numpy(_sparse(1000, 0.03, 1, 2)).to(gpu)
     dense = torch.from_numpy(_sparse(1000, 0.30, 2, 2, symmetric=False)).to(gpu)
     Ls, Ld = D.make_layer(sparse), D.make_layer(dense)

@@ -202,7 +202,8 @@ def test_full_size_c2_properties(gpu):
     assert planted[top].mean() > 0.95
 
 
-def test_full_size_c3_properties(gpu):
+@pytest.mark.parametrize("storage", ["auto", "tiles"])
+def test_full_size_c3_properties(gpu, storage):
     """The configuration the metric is quoted on (BASELINE configs[2]: n = 50 000, 8 weighted layers, top 10 % kept,
     one_vs_rest) at full size, 80 GB resident.  Far beyond the CPU oracle, so the same size-independent properties as
     for C2: singular-pair residuals recomputed with the independent SIMT product, orthogonality of the right factor,
@@ -217,9 +218,12 @@ def test_full_size_c3_properties(gpu):
     layers = []
     for t in range(T):
         raw = D.sbm_generate(n, K, Bs[t], seed=1, layer=t, weighted=True)
-        layers.append(D.preprocess_to_layer(raw, top_percent_keep=10)[0])
+        layers.append(D.preprocess_to_layer(raw, top_percent_keep=10, storage=storage)[0])
         del raw
-    assert all(L.n_planes == 2 and L.symmetric and L.storage == "tiles" for L in layers)     # 2.6 % dense: compressed tiles
+    if storage == "auto":       # 2.6 % dense: row lists (exact fp32 product on the FMA pipes); forced: compressed tiles
+        assert all(L.symmetric and L.storage == "rows" and L.tile_ptr_t is None for L in layers)
+    else:
+        assert all(L.n_planes == 2 and L.symmetric and L.storage == "tiles" for L in layers)
     dims = list(range(4, 25, 2))
     emb, sigma, left, info = D.uase(layers, k, l=l, seed=42, check_dims=dims, want_left=True)
     assert info["converged"] and info["iterations"] <= 40, info
@@ -233,7 +237,7 @@ def test_full_size_c3_properties(gpu):
     angles = D.subspace_sin_angles(emb, emb2, dims)
     assert max(angles.values()) <= 1e-4, (angles, info["angle_bounds"], info2["angle_bounds"])
     del emb2
-    # residuals with the independent SIMT product on dense planes rebuilt from the tiles (checks to_dense as well)
+    # residuals with the independent SIMT product on dense planes rebuilt from the lists / tiles (checks to_dense as well)
     U = (left.double() / torch.from_numpy(np.sqrt(sigma)).to(gpu)).float()
     pad = torch.zeros((n, l), dtype=torch.float32, device=gpu)
     pad[:, :k] = U
