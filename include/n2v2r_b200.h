@@ -325,6 +325,15 @@ int n2v2r_distances(void* stream, const void* d_embed, int dtype, int T, int64_t
 size_t n2v2r_rank_workspace_bytes(int64_t n, int n_cols);
 int n2v2r_rank_borda(void* stream, const double* d_scores, int64_t n, int n_cols, int n_groups,
                      int32_t* d_positions, int64_t* d_borda, void* d_ws, size_t ws_bytes);
+/* The same rank + Borda for callers that cannot allocate device memory (code under CUDA graph capture, serving loops,
+ * harnesses that forbid cudaMalloc): no workspace argument, the sort buffers are a static device array inside the library
+ * (24 MiB held by every GPU that loads it, until exit), and the call allocates nothing.  No counterpart in the reference.
+ * Limit: n * n_cols <= N2V2R_RANK_NOALLOC_MAX_ELEMS, larger shapes are
+ * rejected with N2V2R_EINVAL (use n2v2r_rank_borda).  All calls share the one array: calls that overlap on the GPU race --
+ * order them on one stream.  Same arguments and results (bit-identical) as n2v2r_rank_borda otherwise. */
+#define N2V2R_RANK_NOALLOC_MAX_ELEMS (1 << 20)
+int n2v2r_rank_borda_noalloc(void* stream, const double* d_scores, int64_t n, int n_cols, int n_groups,
+                             int32_t* d_positions, int64_t* d_borda);
 
 /* ------------------------------------------------------------------------------------
  * K11b  sign transfer for the signed ranks.  Replaces signed_transform_single (model_utils.py:7-19) as

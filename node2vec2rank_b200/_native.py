@@ -100,6 +100,7 @@ SIGNATURES = {
     "n2v2r_distances": (_i, [_vp, _vp, _i, _i, _i64, _i, C.POINTER(C.c_int32), C.POINTER(C.c_int32), _i, _i, _vp]),
     "n2v2r_rank_workspace_bytes": (_sz, [_i64, _i]),
     "n2v2r_rank_borda": (_i, [_vp, _vp, _i64, _i, _i, _vp, _vp, _vp, _sz]),
+    "n2v2r_rank_borda_noalloc": (_i, [_vp, _vp, _i64, _i, _i, _vp, _vp]),
     "n2v2r_signed_scores": (_i, [_vp, _vp, _i, _i64, _i, _vp, _vp]),
     "n2v2r_ndcg": (_i, [_vp, _vp, _i64, _i64, _vp, _i64, _vp, _vp]),
     "n2v2r_scatter_edges": (_i, [_vp, _vp, _vp, _vp, _i64, _vp, _i, _i64, _i64]),

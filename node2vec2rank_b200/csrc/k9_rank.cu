@@ -4,6 +4,7 @@
 #include "common.cuh"
 #include <algorithm>
 #include <math.h>
+#include <mutex>
 
 namespace n2v2r {
 
@@ -270,6 +271,59 @@ extern "C" int n2v2r_rank_borda(void* stream, const double* d_scores, int64_t n,
   uint64_t* keys = a.take<uint64_t>((size_t)n_cols * 2 * n);
   uint32_t* idx = a.take<uint32_t>((size_t)n_cols * 2 * n);
   N2V2R_CUDA(cudaMemsetAsync(d_borda, 0, sizeof(int64_t) * n * n_groups, s));
+  const int grid = n_cols < sm_count() * 2 ? n_cols : sm_count() * 2;
+  rank_sort_kernel<<<grid, 1024, 0, s>>>(d_scores, n, n_cols, n_cols / n_groups, keys, idx, d_positions, (unsigned long long*)d_borda);
+  N2V2R_CHECK_LAUNCH();
+  return N2V2R_OK;
+}
+
+// ---- rank + Borda without any allocation by anyone (no counterpart in the reference) ----
+// The sort buffers of n2v2r_rank_borda (two uint64 key arrays and two uint32 index arrays per column) live in a file-scope device
+// array instead of a caller workspace, so a caller that cannot allocate device memory (CUDA graph capture, serving loops,
+// harnesses that forbid cudaMalloc) only passes its inputs and outputs.  Every GPU that loads the library holds the array
+// (24 MiB) until the process exits.  All calls share it: two calls that overlap on the GPU (different streams, different
+// threads) race.  Nothing in it has to start at zero -- rank_sort_kernel writes every key / index word before it reads it -- so
+// the contents a previous call left behind are harmless; the only thing cleared is the caller's Borda table.
+constexpr size_t kRankNoAllocMaxElems = (size_t)N2V2R_RANK_NOALLOC_MAX_ELEMS;                  // n * n_cols
+constexpr size_t kRankNoAllocKeyBytes = kRankNoAllocMaxElems * 2 * sizeof(uint64_t);
+constexpr size_t kRankNoAllocBytes = kRankNoAllocKeyBytes + kRankNoAllocMaxElems * 2 * sizeof(uint32_t);
+static __device__ __align__(256) unsigned char g_rank_scratch[kRankNoAllocBytes];
+
+// In host code `g_rank_scratch` is only a handle of the symbol: its device address is looked up once per device (with that
+// device current) and cached.
+static int rank_scratch_address(unsigned char** out) {
+  constexpr int kMaxDevices = 64;
+  static std::mutex mu;
+  static unsigned char* addr[kMaxDevices] = {};
+  int dev = -1;
+  N2V2R_CUDA(cudaGetDevice(&dev));
+  N2V2R_REQUIRE(dev >= 0 && dev < kMaxDevices, "rank_borda_noalloc: device ordinal %d outside 0..%d", dev, kMaxDevices - 1);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!addr[dev]) {
+    void* p = nullptr;
+    N2V2R_CUDA(cudaGetSymbolAddress(&p, g_rank_scratch));
+    N2V2R_REQUIRE(p != nullptr, "rank_borda_noalloc: the scratch symbol has no device address");
+    addr[dev] = (unsigned char*)p;
+  }
+  *out = addr[dev];
+  return N2V2R_OK;
+}
+
+extern "C" int n2v2r_rank_borda_noalloc(void* stream, const double* d_scores, int64_t n, int n_cols, int n_groups,
+                                        int32_t* d_positions, int64_t* d_borda) {
+  N2V2R_REQUIRE(d_scores && d_borda, "rank_borda_noalloc: null pointer");
+  N2V2R_REQUIRE(n > 0 && n < (1ll << 31) && n_cols >= 1 && n_groups >= 1 && n_cols % n_groups == 0,
+                "rank_borda_noalloc: bad shape (n_cols must be a multiple of n_groups)");
+  N2V2R_REQUIRE((size_t)n <= kRankNoAllocMaxElems && (size_t)n * (size_t)n_cols <= kRankNoAllocMaxElems,
+                "rank_borda_noalloc: n * n_cols = %lld exceeds the built-in scratch of %lld score entries (N2V2R_RANK_NOALLOC_MAX_ELEMS); "
+                "use n2v2r_rank_borda with a caller workspace", (long long)n * n_cols, (long long)kRankNoAllocMaxElems);
+  unsigned char* scratch = nullptr;
+  int rc = rank_scratch_address(&scratch);
+  if (rc) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  uint64_t* keys = (uint64_t*)scratch;
+  uint32_t* idx = (uint32_t*)(scratch + kRankNoAllocKeyBytes);
+  N2V2R_CUDA(cudaMemsetAsync(d_borda, 0, sizeof(int64_t) * n * n_groups, s));     // the caller's output; the scratch needs no clearing
   const int grid = n_cols < sm_count() * 2 ? n_cols : sm_count() * 2;
   rank_sort_kernel<<<grid, 1024, 0, s>>>(d_scores, n, n_cols, n_cols / n_groups, keys, idx, d_positions, (unsigned long long*)d_borda);
   N2V2R_CHECK_LAUNCH();
