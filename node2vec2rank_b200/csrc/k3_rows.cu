@@ -8,7 +8,8 @@
 // around that gather:
 //   * rows are cut into blocks of `rb` rows (one CTA each: rb ~ n / #SMs), columns into panels of `W`;
 //   * the non-zeros of (block b, panel p) form one LIST: a u16 row-pointer header (rb + 1 offsets, padded to 16 bytes) and
-//     the 8-byte entries {column inside the panel, fp32 value} sorted by row, the list padded to 16 bytes;
+//     the 8-byte entries {column inside the panel, fp32 value} sorted by row (inside a row: one column parity first, see
+//     rows_fill_kernel), the list padded to 16 bytes;
 //   * list_ptr[b n_panels + p] is the offset of the list in 16-byte units.
 // One producer thread brings, per stage of a ring, the X panel (W x l fp32: one bulk copy of the contiguous rows) and the list
 // of the CTA's block (one bulk copy); groups of 4 lanes own RPG consecutive rows each, keep their l accumulators per row in
@@ -24,6 +25,12 @@
 namespace n2v2r {
 
 static int g_rows_rpg = 0;       // debug: force the rows per group (0 = heuristic)
+static int g_rows_parity = 1;    // debug: 0 = the builder writes every row's entries in plain column order
+
+constexpr int kRowsWarps = 22;                   // consumer warps of the product kernel; warp kRowsWarps is the producer
+constexpr int kRowsThreads = 32 * (kRowsWarps + 1);
+// rows owned by one group of 4 lanes (consecutive rows): the builder orders the entries by it, the product kernel is compiled for it
+static inline int rows_per_group(int rb) { return (rb + 8 * kRowsWarps - 1) / (8 * kRowsWarps); }
 
 // ---------------------------------------------------------------------------------------------------------------------
 // builder
@@ -103,7 +110,8 @@ __global__ void rows_scan_kernel(const uint32_t* __restrict__ units, int64_t n_l
 
 // one CTA per list: header from the counts, then a warp per row writes its entries in column order
 __global__ void rows_fill_kernel(const float* __restrict__ in, int64_t n, int64_t ld, int rb, int W, int n_panels,
-                                 const uint16_t* __restrict__ counts, const uint32_t* __restrict__ list_ptr, uint4* __restrict__ lists) {
+                                 const uint16_t* __restrict__ counts, const uint32_t* __restrict__ list_ptr, uint4* __restrict__ lists,
+                                 int rpg, int parity_order) {
   extern __shared__ uint32_t ptr_s[];            // rb + 1
   const int64_t li = blockIdx.x;
   const int b = (int)(li / n_panels), p = (int)(li - (int64_t)b * n_panels);
@@ -137,12 +145,47 @@ __global__ void rows_fill_kernel(const float* __restrict__ in, int64_t n, int64_
     if (row >= n) break;
     const float* src = in + row * ld;
     uint32_t at = ptr_s[r];
+    // Two lane groups share every 128-byte phase of the product kernel's gather (lanes 8q .. 8q + 7 = groups 2q, 2q + 1), and
+    // the X rows of two columns of the same parity start in the same half of the banks (row stride l x 4 bytes = an odd
+    // number of 64-byte halves for l = 16, 48, 80): a 2-way bank conflict.  So the rows of even groups list their columns
+    // as even, odd, even, odd, ... and the rows of odd groups as odd, even, odd, even, ... (ascending inside each parity
+    // class; the surplus of the larger class follows): in step i the two groups of a phase then gather from opposite halves
+    // as long as both rows still have columns of both parities.  (l = 32, 64: the kernel swaps the chunk order instead.)
+    if (!parity_order) {
+      for (int c0 = 0; c0 < W; c0 += 32) {
+        const int64_t col = (int64_t)p * W + c0 + lane;
+        const float v = col < n ? __ldg(src + col) : 0.f;
+        const uint32_t m = __ballot_sync(0xffffffffu, v != 0.f);
+        if (v != 0.f) ent[at + __popc(m & ((1u << lane) - 1u))] = make_uint2((uint32_t)(c0 + lane), __float_as_uint(v));
+        at += __popc(m);
+      }
+      continue;
+    }
+    const uint32_t first = (uint32_t)((r / rpg) & 1);                  // parity of the columns that open the row
+    const uint32_t mask_first = first ? 0xAAAAAAAAu : 0x55555555u;      // c0 is even: parity of the column = parity of the lane
+    uint32_t n_cls[2] = {0u, 0u};
     for (int c0 = 0; c0 < W; c0 += 32) {
       const int64_t col = (int64_t)p * W + c0 + lane;
       const float v = col < n ? __ldg(src + col) : 0.f;
       const uint32_t m = __ballot_sync(0xffffffffu, v != 0.f);
-      if (v != 0.f) ent[at + __popc(m & ((1u << lane) - 1u))] = make_uint2((uint32_t)(c0 + lane), __float_as_uint(v));
-      at += __popc(m);
+      n_cls[0] += __popc(m & mask_first);
+      n_cls[1] += __popc(m & ~mask_first);
+    }
+    const uint32_t paired = min(n_cls[0], n_cls[1]);
+    uint32_t k_cls[2] = {0u, 0u};
+    for (int c0 = 0; c0 < W; c0 += 32) {
+      const int64_t col = (int64_t)p * W + c0 + lane;
+      const float v = col < n ? __ldg(src + col) : 0.f;
+      const uint32_t m = __ballot_sync(0xffffffffu, v != 0.f);
+      const uint32_t cls = (((uint32_t)lane & 1u) == first) ? 0u : 1u;
+      const uint32_t mc = cls ? (m & ~mask_first) : (m & mask_first);
+      if (v != 0.f) {
+        const uint32_t k = (cls ? k_cls[1] : k_cls[0]) + __popc(mc & ((1u << lane) - 1u));
+        const uint32_t pos = k < paired ? 2u * k + cls : paired + k;
+        ent[at + pos] = make_uint2((uint32_t)(c0 + lane), __float_as_uint(v));
+      }
+      k_cls[0] += __popc(m & mask_first);
+      k_cls[1] += __popc(m & ~mask_first);
     }
   }
 }
@@ -176,9 +219,6 @@ struct RowsArgs {
   const float* x;
   float* y;
 };
-
-constexpr int kRowsWarps = 22;                   // consumer warps; warp kRowsWarps is the producer
-constexpr int kRowsThreads = 32 * (kRowsWarps + 1);
 
 __device__ __forceinline__ float4 lds128f(uint32_t a) {
   float4 v;
@@ -229,6 +269,9 @@ __global__ void __launch_bounds__(kRowsThreads, 1) rows_product_kernel(const Row
   // ===== consumers: a group of 4 lanes owns RPG consecutive rows; lane t holds columns 4 (t + 4 s) .. + 3, s < L16 =====
   const int g = threadIdx.x >> 2, t = lane & 3;
   const bool have = g < n_groups;
+  // l = 32, 64: every X row starts in the same half of the banks, so the odd group of a phase reads its 64-byte chunks in
+  // swapped order (1, 0, 3, 2) and the two groups never meet in the same half; l = 16, 48, 80: see the builder's entry order
+  const uint32_t swap = (L16 % 2 == 0) ? (uint32_t)(g & 1) : 0u;
   float acc[RPG][4 * L16];
 #pragma unroll
   for (int j = 0; j < RPG; ++j)
@@ -254,7 +297,7 @@ __global__ void __launch_bounds__(kRowsThreads, 1) rows_product_kernel(const Row
           const uint32_t ad = xbase + q.x * row_bytes;
 #pragma unroll
           for (int s = 0; s < L16; ++s) {
-            const float4 x = lds128f(ad + s * 64);
+            const float4 x = lds128f(ad + (((uint32_t)s ^ swap) << 6));
             acc[j][4 * s + 0] = fmaf(v, x.x, acc[j][4 * s + 0]);
             acc[j][4 * s + 1] = fmaf(v, x.y, acc[j][4 * s + 1]);
             acc[j][4 * s + 2] = fmaf(v, x.z, acc[j][4 * s + 2]);
@@ -275,11 +318,12 @@ __global__ void __launch_bounds__(kRowsThreads, 1) rows_product_kernel(const Row
 #pragma unroll
       for (int s = 0; s < L16; ++s) {
         float4 v = make_float4(acc[j][4 * s], acc[j][4 * s + 1], acc[j][4 * s + 2], acc[j][4 * s + 3]);
+        float* d = dst + 16 * ((uint32_t)s ^ swap);
         if (a.accumulate) {
-          const float4 o = *reinterpret_cast<const float4*>(dst + 16 * s);
+          const float4 o = *reinterpret_cast<const float4*>(d);
           v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
         }
-        *reinterpret_cast<float4*>(dst + 16 * s) = v;
+        *reinterpret_cast<float4*>(d) = v;
       }
     }
   }
@@ -328,7 +372,7 @@ int stream_apply_rows(cudaStream_t s, int64_t n, int l, const uint32_t* list_ptr
                 list_cap);
   const size_t smem = a.S * stage + 128;
   const int grid = (int)((n + rb - 1) / rb);
-  int rpg = (rb + 8 * kRowsWarps - 1) / (8 * kRowsWarps);
+  int rpg = rows_per_group(rb);
   if (g_rows_rpg >= rpg && g_rows_rpg <= 3) rpg = g_rows_rpg;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   int rc = mma_events_begin(s, &e0, &e1);
@@ -345,6 +389,7 @@ int stream_apply_rows(cudaStream_t s, int64_t n, int l, const uint32_t* list_ptr
 using namespace n2v2r;
 
 extern "C" void n2v2r__debug_rows_rpg(int rpg) { g_rows_rpg = rpg; }
+extern "C" void n2v2r__debug_rows_parity(int on) { g_rows_parity = on; }
 
 extern "C" size_t n2v2r_rows_counts_bytes(int64_t n, int rows_per_block, int panel_cols) {
   if (n <= 0 || rows_per_block <= 0 || panel_cols <= 0) return 0;
@@ -392,7 +437,7 @@ extern "C" int n2v2r_rows_fill(void* stream, const float* d_in, int64_t n, int64
   const int rb = rows_per_block, W = panel_cols;
   const int64_t nb = (n + rb - 1) / rb, np = (n + W - 1) / W;
   rows_fill_kernel<<<(unsigned)(nb * np), 256, (size_t)(rb + 1) * 4, s>>>(d_in, n, ld, rb, W, (int)np, (const uint16_t*)d_counts, d_list_ptr,
-                                                                        (uint4*)d_lists);
+                                                                        (uint4*)d_lists, rows_per_group(rb), g_rows_parity);
   N2V2R_CHECK_LAUNCH();
   return N2V2R_OK;
 }

@@ -31,6 +31,8 @@ del g
 out = {"n": n, "l": l, "keep": keep, "planes": layer_p.n_planes}
 del layer_p
 torch.cuda.synchronize()
+if "--no-parity" in sys.argv:
+    N.load().n2v2r__debug_rows_parity(ctypes.c_int(0))
 t0 = time.perf_counter()
 Lr = D.make_rows_layer(x32, rows_block=opt("--rb", None), panel_cols=opt("--W", None), max_list_bytes=None)
 torch.cuda.synchronize()

@@ -41,7 +41,7 @@ def test_rows_round_trip(gpu, n, density, symmetric, rb, W):
     hdr_units = ((2 * (rb_ + 1) + 15) // 16)
     assert lp.shape[0] == n_lists + 1 and lp[0] == 0 and lp[-1] == L.n_units and np.all(np.diff(lp) >= hdr_units)
     assert 16 * int(np.diff(lp).max()) == L.list_cap
-    # every list: header offsets ascending from 0 to its entry count, entries sorted by (row, column), columns inside the panel
+    # every list: header offsets ascending from 0 to its entry count, entries sorted by (row, parity class, column)
     raw = L.entries.cpu().numpy().reshape(-1).view(np.uint8)
     for li in (0, n_lists // 2, n_lists - 1):
         blob = raw[16 * lp[li]:16 * lp[li + 1]]
@@ -52,6 +52,19 @@ def test_rows_round_trip(gpu, n, density, symmetric, rb, W):
         block = a[b * rb_:(b + 1) * rb_, p * W_:(p + 1) * W_]
         rr, cc = np.nonzero(block)
         assert hdr[-1] == rr.shape[0]
+        # inside a row: columns alternate in parity (even first for the rows of even lane groups), ascending in each class,
+        # the surplus of the larger class last
+        rpg = -(-rb_ // 176)
+        order = []
+        for r in range(block.shape[0]):
+            cols = np.nonzero(block[r])[0]
+            first = (r // rpg) & 1
+            c0, c1 = cols[(cols & 1) == first], cols[(cols & 1) != first]
+            m = min(len(c0), len(c1))
+            seq = np.empty(2 * m, dtype=np.int64)
+            seq[0::2], seq[1::2] = c0[:m], c1[:m]
+            order.append(np.concatenate([seq, c0[m:], c1[m:]]))
+        cc = np.concatenate(order) if order else cc
         assert np.array_equal(ent[:, 0], cc.astype(np.uint32)) and np.array_equal(ent[:, 1], block[rr, cc].view(np.uint32))
         assert np.array_equal(np.diff(hdr)[:block.shape[0]], np.bincount(rr, minlength=block.shape[0]))
     assert np.array_equal(L.numpy().view(np.uint32), a.view(np.uint32))
