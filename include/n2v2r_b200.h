@@ -162,7 +162,8 @@ int n2v2r_project(void* stream, const void* d_W, int dtype, int64_t rows, int64_
 /* ------------------------------------------------------------------------------------
  * K1d  row lists: the storage of a SPARSE layer for the FMA-pipe product (k3_rows.cu).  The rows are cut into blocks of
  * rows_per_block (one CTA each; <= 528), the columns into panels of panel_cols (multiple of 32).  The non-zeros of
- * (block b, panel p) form one list: a u16 header of rows_per_block + 1 entry offsets (padded to 16 bytes) followed by the
+ * (block b, panel p) form one list: a u16 header of rows_per_block + 1 offsets counted in PAIRS of entries (padded to 16
+ * bytes; a row with an odd number of non-zeros ends with the padding entry {0xFFFFFFFF, 0}) followed by the
  * 8-byte entries {u32 column inside the panel, fp32 value} sorted by row; inside a row the columns alternate in parity
  * (even, odd, even, ... when floor(row_in_block / ceil(rows_per_block / 176)) is even; odd, even, odd, ... otherwise;
  * ascending inside each parity class, the surplus of the larger class last: the order keeps the gathers of paired lane

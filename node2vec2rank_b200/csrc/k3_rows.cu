@@ -7,7 +7,8 @@
 // arithmetic but the GATHER of the X rows (l x 4 bytes of shared-memory reads per 8-byte entry), so the layout is built
 // around that gather:
 //   * rows are cut into blocks of `rb` rows (one CTA each: rb ~ n / #SMs), columns into panels of `W`;
-//   * the non-zeros of (block b, panel p) form one LIST: a u16 row-pointer header (rb + 1 offsets, padded to 16 bytes) and
+//   * the non-zeros of (block b, panel p) form one LIST: a u16 row-pointer header (rb + 1 offsets in PAIRS of entries, padded to
+//     16 bytes; every row is padded to whole pairs so that a group reads two entries with one 16-byte load) and
 //     the 8-byte entries {column inside the panel, fp32 value} sorted by row (inside a row: one column parity first, see
 //     rows_fill_kernel), the list padded to 16 bytes;
 //   * list_ptr[b n_panels + p] is the offset of the list in 16-byte units.
@@ -25,6 +26,7 @@
 namespace n2v2r {
 
 static int g_rows_rpg = 0;       // debug: force the rows per group (0 = heuristic)
+constexpr uint32_t kRowsPad = 0xFFFFFFFFu;   // column of the padding entry that completes the last 16-byte pair of an odd row
 static int g_rows_parity = 1;    // debug: 0 = the builder writes every row's entries in plain column order
 
 constexpr int kRowsWarps = 22;                   // consumer warps of the product kernel; warp kRowsWarps is the producer
@@ -60,8 +62,9 @@ __global__ void rows_sizes_kernel(const uint16_t* __restrict__ counts, int64_t n
   uint32_t cnt = 0;
   if (i < n_lists) {
     const uint16_t* c = counts + (size_t)i * rb;
-    for (int r = 0; r < rb; ++r) cnt += c[r];
-    units[i] = hdr_units + ((cnt + 1) >> 1);
+    uint32_t pairs = 0;
+    for (int r = 0; r < rb; ++r) { cnt += c[r]; pairs += (c[r] + 1u) >> 1; }        // every row is padded to whole 16-byte pairs
+    units[i] = hdr_units + pairs;
   }
   // non-zeros in total (one atomic per warp)
   for (int o = 16; o; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
@@ -121,7 +124,7 @@ __global__ void rows_fill_kernel(const float* __restrict__ in, int64_t n, int64_
     uint32_t carry = 0;
     for (int base = 0; base < rb; base += 32) {
       const int r = base + lane;
-      const uint32_t v = r < rb ? c[r] : 0u;
+      const uint32_t v = r < rb ? ((uint32_t)c[r] + 1u) >> 1 : 0u;          // pairs of entries
       uint32_t incl = v;
       for (int o = 1; o < 32; o <<= 1) {
         const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
@@ -138,13 +141,13 @@ __global__ void rows_fill_kernel(const float* __restrict__ in, int64_t n, int64_
   const uint32_t hdr_bytes = (uint32_t)((2 * (rb + 1) + 15) & ~15);
   for (int r = threadIdx.x; r < (int)(hdr_bytes / 2); r += blockDim.x) hdr[r] = (uint16_t)(r <= rb ? ptr_s[r] : 0u);
   uint2* ent = (uint2*)(list + hdr_bytes);
-  const uint32_t total = ptr_s[rb];
-  if (threadIdx.x == 0 && (total & 1u)) ent[total] = make_uint2(0u, 0u);     // the 8 bytes of padding
   for (int r = warp; r < rb; r += nw) {
     const int64_t row = (int64_t)b * rb + r;
     if (row >= n) break;
     const float* src = in + row * ld;
-    uint32_t at = ptr_s[r];
+    const uint32_t at0 = 2u * ptr_s[r];
+    uint32_t at = at0;
+    if (lane == 0 && (c[r] & 1u)) ent[at0 + c[r]] = make_uint2(kRowsPad, 0u);      // odd row: the second half of its last pair
     // Two lane groups share every 128-byte phase of the product kernel's gather (lanes 8q .. 8q + 7 = groups 2q, 2q + 1), and
     // the X rows of two columns of the same parity start in the same half of the banks (row stride l x 4 bytes = an odd
     // number of 64-byte halves for l = 16, 48, 80): a 2-way bank conflict.  So the rows of even groups list their columns
@@ -201,9 +204,9 @@ __global__ void rows_to_dense_kernel(const uint32_t* __restrict__ list_ptr, cons
   for (int r = warp; r < rb; r += nw) {
     const int64_t row = (int64_t)b * rb + r;
     if (row >= n) break;
-    for (uint32_t e = hdr[r] + lane; e < hdr[r + 1]; e += 32) {
+    for (uint32_t e = 2u * hdr[r] + lane; e < 2u * hdr[r + 1]; e += 32) {
       const uint2 q = ent[e];
-      out[row * ld_out + (int64_t)p * W + q.x] = __uint_as_float(q.y);
+      if (q.x != kRowsPad) out[row * ld_out + (int64_t)p * W + q.x] = __uint_as_float(q.y);
     }
   }
 }
@@ -290,18 +293,32 @@ __global__ void __launch_bounds__(kRowsThreads, 1) rows_product_kernel(const Row
     for (int j = 0; j < RPG; ++j) {
       // one row after the other (the accumulators are registers: the row index must be static); the warp walks row j of its 8
       // groups in step, a group whose row is exhausted idles until the longest row of the warp is done
-      for (uint32_t e = pp[j]; __any_sync(0xffffffffu, e < pp[j + 1]); ++e) {
+      for (uint32_t e = pp[j]; __any_sync(0xffffffffu, e < pp[j + 1]); ++e) {      // e counts 16-byte pairs of entries
         if (e < pp[j + 1]) {
-          const uint2 q = ld_shared_v2(ent + 8u * e);
-          const float v = __uint_as_float(q.y);
-          const uint32_t ad = xbase + q.x * row_bytes;
+          const uint4 q = ld_shared_v4(ent + 16u * e);
+          {
+            const float v = __uint_as_float(q.y);
+            const uint32_t ad = xbase + q.x * row_bytes;
 #pragma unroll
-          for (int s = 0; s < L16; ++s) {
-            const float4 x = lds128f(ad + (((uint32_t)s ^ swap) << 6));
-            acc[j][4 * s + 0] = fmaf(v, x.x, acc[j][4 * s + 0]);
-            acc[j][4 * s + 1] = fmaf(v, x.y, acc[j][4 * s + 1]);
-            acc[j][4 * s + 2] = fmaf(v, x.z, acc[j][4 * s + 2]);
-            acc[j][4 * s + 3] = fmaf(v, x.w, acc[j][4 * s + 3]);
+            for (int s = 0; s < L16; ++s) {
+              const float4 x = lds128f(ad + (((uint32_t)s ^ swap) << 6));
+              acc[j][4 * s + 0] = fmaf(v, x.x, acc[j][4 * s + 0]);
+              acc[j][4 * s + 1] = fmaf(v, x.y, acc[j][4 * s + 1]);
+              acc[j][4 * s + 2] = fmaf(v, x.z, acc[j][4 * s + 2]);
+              acc[j][4 * s + 3] = fmaf(v, x.w, acc[j][4 * s + 3]);
+            }
+          }
+          if (q.z != kRowsPad) {
+            const float v = __uint_as_float(q.w);
+            const uint32_t ad = xbase + q.z * row_bytes;
+#pragma unroll
+            for (int s = 0; s < L16; ++s) {
+              const float4 x = lds128f(ad + (((uint32_t)s ^ swap) << 6));
+              acc[j][4 * s + 0] = fmaf(v, x.x, acc[j][4 * s + 0]);
+              acc[j][4 * s + 1] = fmaf(v, x.y, acc[j][4 * s + 1]);
+              acc[j][4 * s + 2] = fmaf(v, x.z, acc[j][4 * s + 2]);
+              acc[j][4 * s + 3] = fmaf(v, x.w, acc[j][4 * s + 3]);
+            }
           }
         }
       }
@@ -423,7 +440,7 @@ extern "C" int n2v2r_rows_count(void* stream, const float* d_in, int64_t n, int6
   N2V2R_CUDA(cudaMemcpyAsync(&mx, max_units, 4, cudaMemcpyDeviceToHost, s));
   N2V2R_CUDA(cudaMemcpyAsync(&nz, nnz, 8, cudaMemcpyDeviceToHost, s));
   N2V2R_CUDA(cudaStreamSynchronize(s));
-  N2V2R_REQUIRE((mx - hdr_units) * 2u <= 65535u, "rows_count: a (block, panel) list holds more than 65535 entries: the layer is too dense for row lists");
+  N2V2R_REQUIRE(mx - hdr_units <= 65535u, "rows_count: a (block, panel) list holds more than 65535 entry pairs: the layer is too dense for row lists");
   *h_units = (int64_t)total;
   *h_max_list_bytes = (int32_t)(mx * 16u);
   *h_nnz = (int64_t)nz;

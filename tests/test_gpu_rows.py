@@ -41,32 +41,32 @@ def test_rows_round_trip(gpu, n, density, symmetric, rb, W):
     hdr_units = ((2 * (rb_ + 1) + 15) // 16)
     assert lp.shape[0] == n_lists + 1 and lp[0] == 0 and lp[-1] == L.n_units and np.all(np.diff(lp) >= hdr_units)
     assert 16 * int(np.diff(lp).max()) == L.list_cap
-    # every list: header offsets ascending from 0 to its entry count, entries sorted by (row, parity class, column)
+    # every list: header offsets (in pairs of entries) ascending from 0, every row padded to whole pairs with {0xFFFFFFFF, 0},
+    # inside a row the columns alternate in parity (even first for the rows of even lane groups), ascending in each class,
+    # the surplus of the larger class last
     raw = L.entries.cpu().numpy().reshape(-1).view(np.uint8)
+    rpg = -(-rb_ // 176)
     for li in (0, n_lists // 2, n_lists - 1):
         blob = raw[16 * lp[li]:16 * lp[li + 1]]
         hdr = blob[:2 * (rb_ + 1)].view(np.uint16).astype(np.int64)
-        assert hdr[0] == 0 and np.all(np.diff(hdr) >= 0)
-        ent = blob[16 * hdr_units:16 * hdr_units + 8 * hdr[-1]].view(np.uint32).reshape(-1, 2)
+        assert hdr[0] == 0 and np.all(np.diff(hdr) >= 0) and 16 * (hdr_units + hdr[-1]) == blob.shape[0]
+        ent = blob[16 * hdr_units:].view(np.uint32).reshape(-1, 2)
         b, p = divmod(li, -(-n // W_))
         block = a[b * rb_:(b + 1) * rb_, p * W_:(p + 1) * W_]
-        rr, cc = np.nonzero(block)
-        assert hdr[-1] == rr.shape[0]
-        # inside a row: columns alternate in parity (even first for the rows of even lane groups), ascending in each class,
-        # the surplus of the larger class last
-        rpg = -(-rb_ // 176)
-        order = []
-        for r in range(block.shape[0]):
-            cols = np.nonzero(block[r])[0]
+        for r in range(rb_):
+            cols = np.nonzero(block[r])[0] if r < block.shape[0] else np.zeros(0, dtype=np.int64)
             first = (r // rpg) & 1
             c0, c1 = cols[(cols & 1) == first], cols[(cols & 1) != first]
             m = min(len(c0), len(c1))
             seq = np.empty(2 * m, dtype=np.int64)
             seq[0::2], seq[1::2] = c0[:m], c1[:m]
-            order.append(np.concatenate([seq, c0[m:], c1[m:]]))
-        cc = np.concatenate(order) if order else cc
-        assert np.array_equal(ent[:, 0], cc.astype(np.uint32)) and np.array_equal(ent[:, 1], block[rr, cc].view(np.uint32))
-        assert np.array_equal(np.diff(hdr)[:block.shape[0]], np.bincount(rr, minlength=block.shape[0]))
+            want = np.concatenate([seq, c0[m:], c1[m:]])
+            seg = ent[2 * hdr[r]:2 * hdr[r + 1]]
+            assert seg.shape[0] == 2 * ((len(cols) + 1) // 2)
+            assert np.array_equal(seg[:len(cols), 0], want.astype(np.uint32))
+            assert np.array_equal(seg[:len(cols), 1], block[r, want].view(np.uint32) if len(cols) else np.zeros(0, dtype=np.uint32))
+            if len(cols) & 1:
+                assert seg[-1, 0] == 0xFFFFFFFF and seg[-1, 1] == 0
     assert np.array_equal(L.numpy().view(np.uint32), a.view(np.uint32))
     if not L.symmetric:
         Lt = D.DeviceLayer(planes=None, n=n, ld=L.ld, n_planes=3, storage="rows", tile_rows=rb_, panel_cols=W_, tile_ptr=L.tile_ptr_t,
