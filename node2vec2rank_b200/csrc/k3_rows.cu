@@ -19,6 +19,9 @@
 // step (a quarter warp whose two groups are both done costs no shared-memory cycle).  Walking the RPG rows of a group as ONE
 // sequence with the accumulator chosen by predication was measured and lost (0.83 ms against 0.69 ms at C3): the extra FMAs
 // cost more issue slots than the idle steps they save.
+// Also measured and rejected: loading the next pair of entries while the current one is multiplied and issuing both gathers
+// of a pair before the first FMA (software pipelining): 0.666 ms against 0.639 ms -- the kernel sits on the shared-memory
+// wavefronts and the issue slots (ncu: 89 % / 52 %), not on latency, and the extra registers and moves cost more than they hide.
 // The values are the layer's fp32 values: no bf16 plane split, P = 3 layers cost what P = 1 layers cost.
 #include "sparse_common.cuh"
 #include <algorithm>
