@@ -830,6 +830,13 @@ def stream_roofline(env, infos, ms_step, steps, n, n_planes, l, workload, layers
         if isinstance(ent, dict) and (ent.get("n"), ent.get("planes"), ent.get("l")) == (n, n_planes, l):
             roof["traffic"] = ent.get("bytes_per_launch")
             roof["traffic_source"] = ent.get("source")
+            wf = ent.get("shared_wavefronts_per_launch")
+            if wf and "shared_memory_gather" in roof and mma_n:
+                # what actually bounds rows_product_kernel: shared-memory wavefronts (ncu count of the same launch shape, one
+                # per clock and SM at most) over the clocks of the live-timed launch
+                g = roof["shared_memory_gather"]
+                g["wavefronts_per_launch_ncu"] = wf
+                g["wavefront_frac"] = wf / (avg_s * env.sm_max_mhz * 1e6 * env.sm_count)
     except (OSError, ValueError):
         pass
     return roof

@@ -195,7 +195,7 @@ int n2v2r_rows_to_dense(void* stream, const uint32_t* d_list_ptr, const void* d_
 typedef struct {
   const void* d_planes;    /* PLANES: n_planes planes, each n x ld bf16; E4M3: one plane n x ld bytes (ld % 128 == 0) */
   const void* d_planes_t;  /* planes of A^T, or NULL when the layer is symmetric         */
-  int32_t n_planes;        /* planes stored (PLANES) / plane terms the values need (TILES) */
+  int32_t n_planes;        /* planes stored (PLANES) / plane terms the values need (TILES) / unused, 0 (ROWS: fp32 values) */
   int32_t storage;         /* n2v2r_storage_t                                            */
   int64_t ld;
   /* N2V2R_STORE_TILES (see "K1c compressed tiles" below) */

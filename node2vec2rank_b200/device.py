@@ -470,7 +470,7 @@ def make_rows_layer(x32: torch.Tensor, colsum=None, max_density=None, rows_block
             return None
     if colsum is None:
         colsum = x32.sum(dim=0, dtype=torch.float64)
-    return DeviceLayer(planes=None, n=n, ld=(n + 63) // 64 * 64, n_planes=3, symmetric=sym, colsum=colsum, storage="rows",
+    return DeviceLayer(planes=None, n=n, ld=(n + 63) // 64 * 64, n_planes=0, symmetric=sym, colsum=colsum, storage="rows",
                        tile_rows=rb, panel_cols=W, tile_ptr=a[0], entries=a[1], n_units=a[2], list_cap=a[3], n_entries=a[4],
                        tile_ptr_t=None if at is None else at[0], entries_t=None if at is None else at[1],
                        n_units_t=0 if at is None else at[2], list_cap_t=0 if at is None else at[3], n_entries_t=0 if at is None else at[4])

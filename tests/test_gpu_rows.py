@@ -69,7 +69,7 @@ def test_rows_round_trip(gpu, n, density, symmetric, rb, W):
                 assert seg[-1, 0] == 0xFFFFFFFF and seg[-1, 1] == 0
     assert np.array_equal(L.numpy().view(np.uint32), a.view(np.uint32))
     if not L.symmetric:
-        Lt = D.DeviceLayer(planes=None, n=n, ld=L.ld, n_planes=3, storage="rows", tile_rows=rb_, panel_cols=W_, tile_ptr=L.tile_ptr_t,
+        Lt = D.DeviceLayer(planes=None, n=n, ld=L.ld, n_planes=0, storage="rows", tile_rows=rb_, panel_cols=W_, tile_ptr=L.tile_ptr_t,
                            entries=L.entries_t, n_entries=L.n_entries_t, n_units=L.n_units_t, list_cap=L.list_cap_t)
         assert np.array_equal(Lt.numpy(), a.T)
     else:
