@@ -8,7 +8,9 @@ namespace n2v2r {
 
 // ---- X^T Y partials: each CTA reduces a slab of rows into an l x l fp64 block ------------
 // 256 threads as 16 x 16; thread (ag, bg) owns out[ag + 16 i][bg + 16 j], i, j < 5 (l <= 80):
-// 25 fp64 accumulators in registers, per row 5 + 5 shared loads for 25 DFMA.
+// NB x NB fp64 accumulators in registers (NB = ceil(l / 16): the loads, float -> double conversions and DFMAs of column groups
+// beyond l are not issued; the sums are the same bits for every NB), per row NB + NB shared loads for NB^2 DFMA.
+template <int NB>
 __global__ void __launch_bounds__(256) xty_kernel(const float* __restrict__ X, const float* __restrict__ Y, int64_t n, int l,
                                                   int rows_per_cta, double* __restrict__ partials) {
   extern __shared__ float sm[];             // 2 * 32 * l
@@ -17,11 +19,11 @@ __global__ void __launch_bounds__(256) xty_kernel(const float* __restrict__ X, c
   const int64_t r0 = (int64_t)blockIdx.x * rows_per_cta;
   const int64_t r1 = (r0 + rows_per_cta < n) ? r0 + rows_per_cta : n;
   const int ag = threadIdx.x & 15, bg = threadIdx.x >> 4;
-  double acc[5][5];
+  double acc[NB][NB];
 #pragma unroll
-  for (int i = 0; i < 5; ++i)
+  for (int i = 0; i < NB; ++i)
 #pragma unroll
-    for (int j = 0; j < 5; ++j) acc[i][j] = 0.0;
+    for (int j = 0; j < NB; ++j) acc[i][j] = 0.0;
   for (int64_t rb = r0; rb < r1; rb += 32) {
     const int rows = (int)((r1 - rb < 32) ? (r1 - rb) : 32);
     for (int t = threadIdx.x; t < 32 * l; t += 256) {
@@ -32,36 +34,47 @@ __global__ void __launch_bounds__(256) xty_kernel(const float* __restrict__ X, c
     __syncthreads();
 #pragma unroll 4
     for (int r = 0; r < 32; ++r) {
-      double xv[5], yv[5];
+      double xv[NB], yv[NB];
 #pragma unroll
-      for (int i = 0; i < 5; ++i) {
+      for (int i = 0; i < NB; ++i) {
         xv[i] = (ag + 16 * i < l) ? (double)sx[r * l + ag + 16 * i] : 0.0;
         yv[i] = (bg + 16 * i < l) ? (double)sy[r * l + bg + 16 * i] : 0.0;
       }
 #pragma unroll
-      for (int i = 0; i < 5; ++i)
+      for (int i = 0; i < NB; ++i)
 #pragma unroll
-        for (int j = 0; j < 5; ++j) acc[i][j] = fma(xv[i], yv[j], acc[i][j]);
+        for (int j = 0; j < NB; ++j) acc[i][j] = fma(xv[i], yv[j], acc[i][j]);
     }
     __syncthreads();
   }
 #pragma unroll
-  for (int i = 0; i < 5; ++i)
+  for (int i = 0; i < NB; ++i)
 #pragma unroll
-    for (int j = 0; j < 5; ++j) {
+    for (int j = 0; j < NB; ++j) {
       const int a_ = ag + 16 * i, b_ = bg + 16 * j;
       if (a_ < l && b_ < l) partials[(size_t)blockIdx.x * l * l + a_ * l + b_] = acc[i][j];
     }
 }
 
-// fixed-order sum of the per-CTA partials (deterministic)
-__global__ void sum_partials_kernel(const double* __restrict__ partials, int n_parts, int count, double* __restrict__ out,
-                                    int accumulate) {
-  const int e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= count) return;
-  double s = accumulate ? out[e] : 0.0;
-  for (int p = 0; p < n_parts; ++p) s += partials[(size_t)p * count + e];
-  out[e] = s;
+// fixed-order sum of the per-CTA partials (deterministic): 256 threads as 32 elements x 8 slices; slice q adds the partials
+// q, q + 8, q + 16, ... in order (a warp reads 32 consecutive elements of one partial), then the 8 slice sums are added in
+// order.  The order depends only on n_parts, never on timing.
+__global__ void __launch_bounds__(256) sum_partials_kernel(const double* __restrict__ partials, int n_parts, int count,
+                                                           double* __restrict__ out, int accumulate) {
+  __shared__ double slice[8][33];
+  const int el = threadIdx.x & 31, q = threadIdx.x >> 5;
+  const int e = blockIdx.x * 32 + el;
+  double s = 0.0;
+  if (e < count)
+    for (int p = q; p < n_parts; p += 8) s += partials[(size_t)p * count + e];
+  slice[q][el] = s;
+  __syncthreads();
+  if (q == 0 && e < count) {
+    double t = accumulate ? out[e] : 0.0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) t += slice[k][el];
+    out[e] = t;
+  }
 }
 
 // ---- single-CTA dense helpers on l x l fp64 matrices in shared memory ----------------------
@@ -296,7 +309,8 @@ __global__ void __launch_bounds__(512) smallmat_kernel(int mode, int l, const do
 }
 
 // ---- Out[n][lo] = X[n][l] * C[l][lo], fp64 accumulate -----------------------------------------
-// 256 threads as 16 (row groups of 4) x 16 (column groups: j = cg + 16 q, q < 5); tile = 64 rows.
+// 256 threads as 16 (row groups of 4) x 16 (column groups: j = cg + 16 q, q < QB = ceil(lo / 16)); tile = 64 rows.
+template <int QB>
 __global__ void __launch_bounds__(256) apply_small_kernel(const float* __restrict__ X, int64_t n, int l, const double* __restrict__ C,
                                                           int ldc, int lo, float* __restrict__ Out, int64_t ld_out) {
   extern __shared__ double sd[];
@@ -312,28 +326,28 @@ __global__ void __launch_bounds__(256) apply_small_kernel(const float* __restric
       sx[r * ls + c] = (rb + r < n) ? X[(rb + r) * l + c] : 0.f;
     }
     __syncthreads();
-    double acc[4][5];
+    double acc[4][QB];
 #pragma unroll
     for (int i = 0; i < 4; ++i)
 #pragma unroll
-      for (int q = 0; q < 5; ++q) acc[i][q] = 0.0;
+      for (int q = 0; q < QB; ++q) acc[i][q] = 0.0;
     for (int k = 0; k < l; ++k) {
-      double xv[4], cv[5];
+      double xv[4], cv[QB];
 #pragma unroll
       for (int i = 0; i < 4; ++i) xv[i] = (double)sx[(rg * 4 + i) * ls + k];
 #pragma unroll
-      for (int q = 0; q < 5; ++q) cv[q] = (cg + 16 * q < lo) ? sC[k * lo + cg + 16 * q] : 0.0;
+      for (int q = 0; q < QB; ++q) cv[q] = (cg + 16 * q < lo) ? sC[k * lo + cg + 16 * q] : 0.0;
 #pragma unroll
       for (int i = 0; i < 4; ++i)
 #pragma unroll
-        for (int q = 0; q < 5; ++q) acc[i][q] = fma(xv[i], cv[q], acc[i][q]);
+        for (int q = 0; q < QB; ++q) acc[i][q] = fma(xv[i], cv[q], acc[i][q]);
     }
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       const int64_t row = rb + rg * 4 + i;
       if (row < n) {
 #pragma unroll
-        for (int q = 0; q < 5; ++q)
+        for (int q = 0; q < QB; ++q)
           if (cg + 16 * q < lo) Out[row * ld_out + cg + 16 * q] = (float)acc[i][q];
       }
     }
@@ -446,9 +460,15 @@ int launch_xty(cudaStream_t s, const float* X, const float* Y, int64_t n, int l,
   int rows_per_cta = (int)((n + parts - 1) / parts);
   rows_per_cta = (rows_per_cta + 31) / 32 * 32;
   parts = (int)((n + rows_per_cta - 1) / rows_per_cta);
-  xty_kernel<<<parts, 256, sizeof(float) * 64 * l, s>>>(X, Y, n, l, rows_per_cta, partials);
+  switch ((l + 15) / 16) {
+    case 1: xty_kernel<1><<<parts, 256, sizeof(float) * 64 * l, s>>>(X, Y, n, l, rows_per_cta, partials); break;
+    case 2: xty_kernel<2><<<parts, 256, sizeof(float) * 64 * l, s>>>(X, Y, n, l, rows_per_cta, partials); break;
+    case 3: xty_kernel<3><<<parts, 256, sizeof(float) * 64 * l, s>>>(X, Y, n, l, rows_per_cta, partials); break;
+    case 4: xty_kernel<4><<<parts, 256, sizeof(float) * 64 * l, s>>>(X, Y, n, l, rows_per_cta, partials); break;
+    default: xty_kernel<5><<<parts, 256, sizeof(float) * 64 * l, s>>>(X, Y, n, l, rows_per_cta, partials); break;
+  }
   N2V2R_CHECK_LAUNCH();
-  sum_partials_kernel<<<(l * l + 255) / 256, 256, 0, s>>>(partials, parts, l * l, out, accumulate);
+  sum_partials_kernel<<<(l * l + 31) / 32, 256, 0, s>>>(partials, parts, l * l, out, accumulate);
   N2V2R_CHECK_LAUNCH();
   return N2V2R_OK;
 }
@@ -469,13 +489,23 @@ int launch_apply_small(cudaStream_t s, const float* X, int64_t n, int l, const d
   static bool done = false;
   const size_t max_smem = sizeof(double) * kMaxL * kMaxL + sizeof(float) * 64 * (kMaxL + 1);
   if (!done) {
-    N2V2R_CUDA(cudaFuncSetAttribute(apply_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)max_smem));
+    N2V2R_CUDA(cudaFuncSetAttribute(apply_small_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)max_smem));
+    N2V2R_CUDA(cudaFuncSetAttribute(apply_small_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)max_smem));
+    N2V2R_CUDA(cudaFuncSetAttribute(apply_small_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)max_smem));
+    N2V2R_CUDA(cudaFuncSetAttribute(apply_small_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)max_smem));
+    N2V2R_CUDA(cudaFuncSetAttribute(apply_small_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)max_smem));
     done = true;
   }
   const int64_t tiles = (n + 63) / 64;
   const int grid = (int)(tiles < (int64_t)sm_count() * 4 ? tiles : (int64_t)sm_count() * 4);
   const size_t smem = sizeof(double) * (size_t)l * lo + sizeof(float) * 64 * (l + 1);
-  apply_small_kernel<<<grid, 256, smem, s>>>(X, n, l, C, ldc, lo, Out, ld_out);
+  switch ((lo + 15) / 16) {
+    case 1: apply_small_kernel<1><<<grid, 256, smem, s>>>(X, n, l, C, ldc, lo, Out, ld_out); break;
+    case 2: apply_small_kernel<2><<<grid, 256, smem, s>>>(X, n, l, C, ldc, lo, Out, ld_out); break;
+    case 3: apply_small_kernel<3><<<grid, 256, smem, s>>>(X, n, l, C, ldc, lo, Out, ld_out); break;
+    case 4: apply_small_kernel<4><<<grid, 256, smem, s>>>(X, n, l, C, ldc, lo, Out, ld_out); break;
+    default: apply_small_kernel<5><<<grid, 256, smem, s>>>(X, n, l, C, ldc, lo, Out, ld_out); break;
+  }
   N2V2R_CHECK_LAUNCH();
   return N2V2R_OK;
 }
@@ -490,7 +520,7 @@ int launch_resid(cudaStream_t s, const float* Yw, const float* Qw, int64_t n, in
   parts = (int)((n + rows_per_cta - 1) / rows_per_cta);
   resid_kernel<<<parts, 256, 0, s>>>(Yw, Qw, n, l, lam, rows_per_cta, partials);
   N2V2R_CHECK_LAUNCH();
-  sum_partials_kernel<<<(l + 255) / 256, 256, 0, s>>>(partials, parts, l, out, 0);
+  sum_partials_kernel<<<(l + 31) / 32, 256, 0, s>>>(partials, parts, l, out, 0);
   N2V2R_CHECK_LAUNCH();
   return N2V2R_OK;
 }
@@ -511,7 +541,7 @@ int launch_sub_proj(cudaStream_t s, float* X, const float* U, int64_t n, int l, 
 }
 
 int launch_sum_partials(cudaStream_t s, const double* partials, int n_parts, int count, double* out) {
-  sum_partials_kernel<<<(count + 255) / 256, 256, 0, s>>>(partials, n_parts, count, out, 0);
+  sum_partials_kernel<<<(count + 31) / 32, 256, 0, s>>>(partials, n_parts, count, out, 0);
   N2V2R_CHECK_LAUNCH();
   return N2V2R_OK;
 }
