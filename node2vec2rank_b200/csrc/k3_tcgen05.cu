@@ -21,6 +21,8 @@ struct StreamArgs {
   int n_jb;                         // column blocks of width l of the right operand (1 for the skinny products)
   int nb;                           // operand blocks multiplied against ONE read of the A tile (seed batching; 1 otherwise)
   int upper_only;                   // SYRK: skip units entirely below the diagonal (projection)
+  int col_batched;                  // projection: the nb operand blocks of a unit are the column blocks jb nb .. jb nb + nb - 1 of ONE
+                                    // operand (one TMA load each); 0: seed batching, the blocks are stacked operands (one load)
   int64_t k_pad;                    // contraction length, multiple of 64
   int64_t rows_valid, cols_valid;   // extent of the output that may be written
   int64_t out_ld, split_stride;     // output leading dimension / elements between K-split partials
@@ -70,14 +72,19 @@ __global__ void __launch_bounds__(192, 1) stream_mma_kernel(const __grid_constan
         const int64_t k_begin = (int64_t)split * a.k_chunk;
         const int64_t k_end = (k_begin + a.k_chunk < a.k_pad) ? k_begin + a.k_chunk : a.k_pad;
         const int row0 = tile * 128 * a.mh;
-        if (a.upper_only && (jb + 1) * a.l <= row0) continue;
+        if (a.upper_only && (jb + 1) * (a.col_batched ? a.nb : 1) * a.l <= row0) continue;
         for (int64_t k0 = k_begin; k0 < k_end; k0 += 64) {
           mbar_wait(bar_empty + 8 * stage, phase ^ 1u);
           const uint32_t base = smem0 + stage * a.stage_bytes;
           mbar_expect_tx(bar_full + 8 * stage, a.stage_bytes);
           for (int p = 0; p < a.n_planes; ++p)
             tma_load_2d(maps[p], bar_full + 8 * stage, base + p * a.a_plane_bytes, (int)k0, row0);
-          tma_load_3d(&mapX, bar_full + 8 * stage, base + a.n_planes * a.a_plane_bytes, (int)k0, jb * a.l, 0);
+          if (a.col_batched) {
+            for (int bk = 0; bk < a.nb; ++bk)
+              tma_load_3d(&mapX, bar_full + 8 * stage, base + a.n_planes * a.a_plane_bytes + bk * a.x_bytes, (int)k0, (jb * a.nb + bk) * a.l, 0);
+          } else {
+            tma_load_3d(&mapX, bar_full + 8 * stage, base + a.n_planes * a.a_plane_bytes, (int)k0, jb * a.l, 0);
+          }
           if (++stage == a.stages) { stage = 0; phase ^= 1u; }
         }
       }
@@ -88,7 +95,7 @@ __global__ void __launch_bounds__(192, 1) stream_mma_kernel(const __grid_constan
     for (int u = blockIdx.x; u < n_units; u += gridDim.x) {
       const int sj_ = u / a.n_tiles;
       const int split = sj_ / a.n_jb;
-      if (a.upper_only && ((sj_ - split * a.n_jb) + 1) * a.l <= (u - sj_ * a.n_tiles) * 128 * a.mh) continue;
+      if (a.upper_only && ((sj_ - split * a.n_jb) + 1) * (a.col_batched ? a.nb : 1) * a.l <= (u - sj_ * a.n_tiles) * 128 * a.mh) continue;
       const int64_t k_begin = (int64_t)split * a.k_chunk;
       const int64_t k_end = (k_begin + a.k_chunk < a.k_pad) ? k_begin + a.k_chunk : a.k_pad;
       mbar_wait(bar_tempty, uphase ^ 1u);            // epilogue has drained the accumulators
@@ -149,14 +156,15 @@ __global__ void __launch_bounds__(192, 1) stream_mma_kernel(const __grid_constan
     for (int u = blockIdx.x; u < n_units; u += gridDim.x) {
       const int sj = u / a.n_tiles, tile = u - sj * a.n_tiles;
       const int split = sj / a.n_jb, jb = sj - split * a.n_jb;
-      if (a.upper_only && (jb + 1) * a.l <= tile * 128 * a.mh) continue;
+      if (a.upper_only && (jb + 1) * (a.col_batched ? a.nb : 1) * a.l <= tile * 128 * a.mh) continue;
       mbar_wait(bar_tfull, uphase);
       tc_fence_after();
       for (int bk = 0; bk < a.nb; ++bk)
       for (int h = 0; h < a.mh; ++h) {
         const int64_t row = (int64_t)tile * 128 * a.mh + h * 128 + q * 32 + lane;
-        float* dst = a.out + (size_t)split * a.split_stride + (size_t)row * a.out_ld + (size_t)(jb + bk) * a.l;
-        const int64_t col_base = (int64_t)(jb + bk) * a.l;
+        const int jcol = a.col_batched ? jb * a.nb + bk : jb + bk;
+        float* dst = a.out + (size_t)split * a.split_stride + (size_t)row * a.out_ld + (size_t)jcol * a.l;
+        const int64_t col_base = (int64_t)jcol * a.l;
         const bool row_ok = row < a.rows_valid;
         const bool vec_ok = row_ok && (a.out_ld % 4 == 0) && (col_base + a.l <= a.cols_valid);
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (bk * a.mh + h) * nacc;
@@ -354,9 +362,10 @@ int make_map_u8(CUtensorMap* map, const void* base, int rank, const uint64_t* di
 static int launch_mma(cudaStream_t s, const void* a_planes, int n_planes, int64_t m_rows, int64_t lda, size_t a_plane_stride,
                       const void* b_planes, int64_t b_rows, int64_t ldb, int l, int n_jb, int64_t k_pad, int k_chunk,
                       float* out, int64_t out_ld, int64_t split_stride, int64_t rows_valid, int64_t cols_valid, int upper_only = 0,
-                      int nb = 1) {
+                      int nb = 1, int col_batched = 0) {
   StreamArgs a;
   a.upper_only = upper_only;
+  a.col_batched = col_batched;
   a.n_planes = n_planes;
   a.l = l;
   a.nb = nb;
@@ -365,7 +374,7 @@ static int launch_mma(cudaStream_t s, const void* a_planes, int n_planes, int64_
   a.k_chunk = k_chunk;
   a.k_pad = k_pad;
   a.n_splits = (int)((k_pad + k_chunk - 1) / k_chunk);
-  a.n_jb = n_jb;
+  a.n_jb = col_batched ? (n_jb + nb - 1) / nb : n_jb;
   a.n_tiles = (int)((m_rows + 128 * a.mh - 1) / (128 * a.mh));
   a.a_plane_bytes = 16384u * a.mh;
   a.x_bytes = 3u * l * 128u;                       // multiple of 1024 because l % 16 == 0
@@ -389,9 +398,10 @@ static int launch_mma(cudaStream_t s, const void* a_planes, int n_planes, int64_
     if (rc) return rc;
   }
   {
-    const uint64_t dims[3] = {(uint64_t)ldb, (uint64_t)b_rows, (uint64_t)(3 * nb)};     // batched: [nb][3][l][ldb], b_rows == l
+    const int stacked = col_batched ? 1 : nb;                                           // seed batching: [nb][3][l][ldb], b_rows == l
+    const uint64_t dims[3] = {(uint64_t)ldb, (uint64_t)b_rows, (uint64_t)(3 * stacked)};
     const uint64_t str[2] = {(uint64_t)ldb * 2, (uint64_t)b_rows * ldb * 2};
-    const uint32_t box[3] = {64, (uint32_t)l, (uint32_t)(3 * nb)};
+    const uint32_t box[3] = {64, (uint32_t)l, (uint32_t)(3 * stacked)};
     int rc = make_map(&mX, b_planes, 3, dims, str, box);
     if (rc) return rc;
   }
@@ -478,6 +488,13 @@ using namespace n2v2r;
 
 // K2: out = W^T W (on_rows=0) or W W^T (on_rows=1) -- preprocessing_utils.py:16-32
 static const int kProjChunk = 512;     // K-split of the projection: short fp32 accumulation chains in TMEM, partials summed in order
+static int g_proj_chunk = kProjChunk;  // debug knobs (n2v2r__debug_project): K chunk actually used (<= kProjChunk splits fit the workspace) ...
+static int g_proj_nb = 2;              // ... and column blocks per A tile read
+
+extern "C" void n2v2r__debug_project(int k_chunk, int nb) {
+  if (k_chunk >= kProjChunk && k_chunk % 64 == 0) g_proj_chunk = k_chunk;
+  if (nb >= 1 && nb <= 2) g_proj_nb = nb;
+}
 
 extern "C" size_t n2v2r_project_workspace_bytes(int64_t rows, int64_t cols, int on_rows) {
   const int64_t m = on_rows ? rows : cols, k = on_rows ? cols : rows;
@@ -494,7 +511,7 @@ extern "C" int n2v2r_project(void* stream, const void* d_W, int dtype, int64_t r
   if (ws_bytes < n2v2r_project_workspace_bytes(rows, cols, on_rows)) { set_error("project: workspace too small"); return N2V2R_ENOMEM; }
   cudaStream_t s = (cudaStream_t)stream;
   const int64_t k_pad = round_up(k, 64);
-  const int n_splits = (int)((k_pad + kProjChunk - 1) / kProjChunk);
+  const int n_splits = (int)((k_pad + g_proj_chunk - 1) / g_proj_chunk);
   const int64_t m_pad = round_up(m, 256);
   __nv_bfloat16* Ws = (__nv_bfloat16*)d_ws;
   float* parts = (float*)((char*)d_ws + align_up(sizeof(__nv_bfloat16) * 3 * (size_t)m * k_pad));
@@ -508,8 +525,9 @@ extern "C" int n2v2r_project(void* stream, const void* d_W, int dtype, int64_t r
   const int l = 64;
   const int n_jb = (int)((m + l - 1) / l);
   // SYRK: only units touching the upper triangle are computed; the mirror kernel fills the rest
-  int rc = launch_mma(s, Ws, 3, m, k_pad, (size_t)m * k_pad * sizeof(__nv_bfloat16), Ws, m, k_pad, l, n_jb, k_pad, kProjChunk,
-                      parts, m, m_pad * m, m, m, 1);
+  // two column blocks per read of the A tile (A k-slices kept in the collector): the unit's A traffic per output column halves
+  int rc = launch_mma(s, Ws, 3, m, k_pad, (size_t)m * k_pad * sizeof(__nv_bfloat16), Ws, m, k_pad, l, n_jb, k_pad, g_proj_chunk,
+                      parts, m, m_pad * m, m, m, 1, g_proj_nb, g_proj_nb > 1 ? 1 : 0);
   if (rc) return rc;
   const unsigned tiles = (unsigned)((m + 31) / 32);
   mirror_reduce_kernel<<<dim3(tiles, tiles), 256, 0, s>>>(parts, n_splits, m_pad * m, m, d_out, ld_out);
