@@ -115,10 +115,11 @@ def _run_shape(gpu, workload, n, storage, l=48):
     return info, cross
 
 
-@pytest.mark.parametrize("storage", ["tiles", "planes"])
+@pytest.mark.parametrize("storage", ["rows", "tiles", "planes"])
 def test_c3_in_miniature(gpu, storage):
     """BASELINE configs[2] (the configuration the metric is quoted on) at n = 6000: 8 weighted layers, K = 32, top 10 %
-    kept (2.6 % dense, 16-bit weights -> 2 planes), one_vs_rest, d = 4..24, euclidean + cosine, Borda; both layer storages."""
+    kept (2.6 % dense, 16-bit weights -> 2 planes), one_vs_rest, d = 4..24, euclidean + cosine, Borda; the three layer
+    storages a sparse layer can have (row lists are what the full-size benchmark runs on)."""
     info, cross = _run_shape(gpu, "c3", 6000, storage)
     assert info["iterations"] <= 80
 
