@@ -67,7 +67,8 @@ def parse_args():
     ap.add_argument("--host-transfer", default="auto", choices=["auto", "dense", "packed"],
                     help="e2e leg: how the host float32 graphs cross PCIe (device.layers_from_host)")
     ap.add_argument("--n", type=int, default=0, help="override the node count (development only; named in config.workload)")
-    ap.add_argument("--block-width", type=int, default=48, help="solver block width l (default = device.default_block_width(24, n))")
+    ap.add_argument("--block-width", type=int, default=0,
+                    help="solver block width l (default 0 = device.default_block_width(24, n, storage): 32 on row-list layers, 48 otherwise)")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer end-to-end leg (development only)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (development only)")
     ap.add_argument("--layer-storage", default="auto", choices=["auto", "planes", "tiles", "e4m3", "rows"],
@@ -613,6 +614,8 @@ def run_b200_arm(args):
     torch.cuda.synchronize()
     n_planes = layers[0].n_planes if layers else 0
     storage = layers[0].storage if layers else "planes"
+    if not l:                                      # default block width: by the layers' storage (the same on every rank)
+        l = D.default_block_width(max(DIMS), n, storage)
     setup_s = time.perf_counter() - t_setup
     preprocess_ms = float(np.mean([a.elapsed_time(b) for a, b in pre_events][1:] or [a.elapsed_time(b) for a, b in pre_events]))
     layers_gb = sum(L.nbytes for L in layers) * (world if slab_rows is not None else T / max(len(layers), 1)) / 1e9
@@ -852,7 +855,7 @@ def run_b200_c5(args, w):
     from node2vec2rank_b200.stability import StabilityRun
 
     env = Env()
-    n, T, K, l, seeds = w["n"], w["T"], w["K"], args.block_width, w["seeds"]
+    n, T, K, l, seeds = w["n"], w["T"], w["K"], args.block_width or 48, w["seeds"]
     mine = [seeds[i] for i in ND.layer_partition(len(seeds), env.world, env.rank)]
     Bs = block_probabilities(w)
     t_setup = time.perf_counter()
@@ -984,10 +987,12 @@ def run_b200_c4(args, w):
             proj_events.append((a, b))
             layers.append(D.preprocess_to_layer(P, top_percent_keep=w["keep"])[0])
             del P
-        emb, _, _, info = D.uase(layers, max(DIMS), l=l, tol=1e-5, max_iters=400, seed=SOLVER_SEED, check_dims=DIMS)
+        lw = l or D.default_block_width(max(DIMS), n, layers[0].storage)
+        emb, _, _, info = D.uase(layers, max(DIMS), l=lw, tol=1e-5, max_iters=400, seed=SOLVER_SEED, check_dims=DIMS)
         scores = D.distances(emb, cdims, cmets, strategy)
         borda = D.rank_borda(scores)[0]
         info["n_planes"] = layers[0].n_planes
+        info["block_width"], info["layer_storage"] = lw, layers[0].storage
         return info, borda, info["kernel_launches"] + 2 + T * 12
 
     ms_step, results, clocks = env.timed(step, args.steps, args.warmup)
@@ -1003,13 +1008,13 @@ def run_b200_c4(args, w):
                 "share_of_step": proj_ms * T / ms_step,
                 "note": "algorithmic 2*r*c*n_out FLOP of the full product; the kernel issues 6 bf16 MMA terms (3x3 split, 6 kept) on "
                         "the upper triangle only, i.e. 3x the algorithmic MMA work",
-                "streaming_products": stream_roofline(env, infos, ms_step, args.steps, n, infos[-1]["n_planes"], l, args.workload)}
+                "streaming_products": stream_roofline(env, infos, ms_step, args.steps, n, infos[-1]["n_planes"], infos[-1]["block_width"], args.workload)}
     e2e = None
     if not args.no_e2e:
         del Ws
         torch.cuda.empty_cache()
         cfg = dict(embed_dimensions=DIMS, distance_metrics=METRICS, comp_strategy=w["strategy"], seed=SOLVER_SEED, save_dir=None,
-                   verbose=-1, block_width=l)
+                   verbose=-1, block_width=l or None)
 
         def e2e_step():
             graphs = [network_transform_device(h.numpy(), top_percent_keep=w["keep"], project_unipartite_on="columns")[0] for h in hosts]
@@ -1031,7 +1036,8 @@ def run_b200_c4(args, w):
         "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": False, "scaling": "strong", "vs_baseline": None,
         "dtype": "projection: 3x3 split-bf16 (6 terms) fp32 accumulate (tcgen05); solve: bf16 planes x3-split operand; fp64 small dense",
         "data": "synthetic",
-        "config": {"workload": w["name"], "n": n, "bipartite_rows": r, "layers": T, "communities": K, "block_width": l,
+        "config": {"workload": w["name"], "n": n, "bipartite_rows": r, "layers": T, "communities": K, "block_width": infos[-1]["block_width"],
+                   "layer_storage": infos[-1]["layer_storage"],
                    "planes_per_layer": last["n_planes"], "l2_policy": "inputs larger than L2 (each projected layer is 3.6 GB fp32)",
                    "operator_applications": last["iterations"], "layer_passes": last["layer_passes"], "converged": last["converged"],
                    "angle_bound": last["angle_bound"], "projection_ms_per_layer": proj_ms, "solver_ms": last["total_ms"], "setup_s": setup_s},

@@ -1039,9 +1039,17 @@ def signed_scores(scores: torch.Tensor, prior: torch.Tensor):
 MAX_EMBED_DIM = 72        # block width l <= 80 (TMEM holds two 3l-column accumulators) minus at least 8 guard vectors
 
 
-def default_block_width(k, n):
-    """Solver block width l: k plus a buffer of guard vectors, a multiple of 16 in [16, 80], < n when possible."""
-    l = ((k + 24 + 15) // 16) * 16
+ROWS_GUARD_VECTORS = 8    # guard vectors of the solver block on row-list layers (24 elsewhere)
+
+
+def default_block_width(k, n, storage=None):
+    """Solver block width l: k plus a buffer of guard vectors, a multiple of 16 in [16, 80], < n when possible.
+    The dense / tile / e4m3 products cost the same for any l <= 64 (they are bound by the layer stream or the A-operand
+    feed), so their block carries 24 guard vectors and needs fewer operator applications; the row-list product is linear
+    in l (it is bound by the gather of l x 4 bytes per entry), where 8 guard vectors win: C3 takes 13 applications at
+    l = 32 against 11 at l = 48, 102 ms against 120 ms, to the same subspace (scripts/probe_c3_solver.py)."""
+    guard = ROWS_GUARD_VECTORS if storage == "rows" else 24
+    l = ((k + guard + 15) // 16) * 16
     l = max(16, min(80, l))
     while l > 16 and l >= n:
         l -= 16

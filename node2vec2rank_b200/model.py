@@ -146,11 +146,15 @@ class N2V2R:
         if k > D.MAX_EMBED_DIM:
             raise NotImplementedError(f"max(embed_dimensions) = {k}: the B200 solver works on blocks of at most 80 vectors "
                                       f"(k + >= 8 guard vectors), i.e. embedding dimensions up to {D.MAX_EMBED_DIM}")
-        l = int(self.config.get("block_width") or D.default_block_width(k, n))
+        storages = {L.storage for L in layers}
+        l = int(self.config.get("block_width") or D.default_block_width(k, n, "rows" if storages == {"rows"} else None))
         T_global, offset = len(layers), 0
         sharded = bool(self.config.get("layer_sharded")) and dist.is_distributed()
         if sharded:
             T_global, offset = self._global_layers(layers)
+            lw = torch.tensor([l], device=N.require_gpu())
+            torch.distributed.all_reduce(lw, op=torch.distributed.ReduceOp.MAX)      # every rank must use the same block
+            l = int(lw.item())
         emb, sigma, _, info = D.uase(layers, k, l=l, tol=float(self.config.get("solver_tol", 1e-5)),
                                      max_iters=int(self.config.get("solver_max_iters", 400)),
                                      seed=self._solver_seed(), check_dims=self.embed_dimensions,

@@ -20,6 +20,8 @@ def test_column_specs_order_and_skip():
 def test_default_block_width():
     from node2vec2rank_b200 import device as D
     assert D.default_block_width(24, 50000) == 48
+    assert D.default_block_width(24, 50000, "rows") == 32        # the row-list product is linear in l: 8 guard vectors
+    assert D.default_block_width(70, 10**6, "rows") == 80 and D.default_block_width(24, 50000, "tiles") == 48
     assert D.default_block_width(8, 1000) == 32
     assert D.default_block_width(70, 10**6) == 80
     assert D.default_block_width(4, 20) == 16
