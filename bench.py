@@ -794,7 +794,7 @@ def stream_roofline(env, infos, ms_step, steps, n, n_planes, l, workload, layers
                         "beside it): the layer crosses HBM as row lists of its non-zeros (exact fp32 values) and is multiplied entry by "
                         "entry on the FMA pipes; the launch is bound by the shared-memory gather of the operand rows (l x 4 bytes per "
                         "8-byte entry), not by HBM, so the HBM fraction is low by construction"}
-        key = f"{workload}_rows_bytes_per_launch"
+        key = f"{workload}_rows_bytes_per_launch" if l == 32 else f"{workload}_rows_l{l}_bytes_per_launch"
     elif tiles:
         L = layers[0]
         terms = {1: 3, 2: 5, 3: 6}[n_planes]
