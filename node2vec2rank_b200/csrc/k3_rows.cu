@@ -22,6 +22,9 @@
 // Also measured and rejected: loading the next pair of entries while the current one is multiplied and issuing both gathers
 // of a pair before the first FMA (software pipelining): 0.666 ms against 0.639 ms -- the kernel sits on the shared-memory
 // wavefronts and the issue slots (ncu: 89 % / 52 %), not on latency, and the extra registers and moves cost more than they hide.
+// Row blocks of half the size with two CTAs per SM (one row per lane group, 44 consumer warps per SM; taken when a layer is built
+// with more row blocks than SMs) gain 3 % at l = 32 (0.451 against 0.463 ms) and lose at l = 48, where two CTAs' stages no longer
+// fit: the builder's default stays one block per SM.
 // The values are the layer's fp32 values: no bf16 plane split, P = 3 layers cost what P = 1 layers cost.
 #include "sparse_common.cuh"
 #include <algorithm>
@@ -30,6 +33,7 @@ namespace n2v2r {
 
 static int g_rows_rpg = 0;       // debug: force the rows per group (0 = heuristic)
 constexpr uint32_t kRowsPad = 0xFFFFFFFFu;   // column of the padding entry that completes the last 16-byte pair of an odd row
+static int g_rows_two_per_sm = 1;   // debug: 0 = never two CTAs per SM
 static int g_rows_parity = 1;    // debug: 0 = the builder writes every row's entries in plain column order
 
 constexpr int kRowsWarps = 22;                   // consumer warps of the product kernel; warp kRowsWarps is the producer
@@ -233,7 +237,7 @@ __device__ __forceinline__ float4 lds128f(uint32_t a) {
 }
 
 template <int L16, int RPG>
-__global__ void __launch_bounds__(kRowsThreads, 1) rows_product_kernel(const RowsArgs a) {
+__global__ void __launch_bounds__(kRowsThreads, (RPG == 1 && L16 <= 3) ? 2 : 1) rows_product_kernel(const RowsArgs a) {
   extern __shared__ __align__(128) uint8_t smem_rows[];
   __shared__ __align__(8) uint64_t bars[16];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -386,14 +390,17 @@ int stream_apply_rows(cudaStream_t s, int64_t n, int l, const uint32_t* list_ptr
   a.list_cap = (list_cap + 127) & ~127;
   a.list_ptr = list_ptr; a.lists = (const uint4*)lists; a.x = x; a.y = out;
   const size_t stage = (size_t)W * l * 4 + a.list_cap;
-  const size_t budget = 227 * 1024 - 1024 - 256;
+  const int grid = (int)((n + rb - 1) / rb);
+  int rpg = rows_per_group(rb);
+  if (g_rows_rpg >= rpg && g_rows_rpg <= 3) rpg = g_rows_rpg;
+  // more row blocks than SMs, one row per lane group and l <= 48: two CTAs share an SM (44 consumer warps instead of 22 hide
+  // the latency of the two dependent shared-memory reads per entry), each with half of the shared memory
+  const bool two_per_sm = g_rows_two_per_sm && rpg == 1 && l <= 48 && grid > sm_count() && 2 * stage + 128 <= 112 * 1024;
+  const size_t budget = two_per_sm ? (size_t)112 * 1024 - 128 : (size_t)227 * 1024 - 1024 - 256;
   a.S = (int)std::min<size_t>(8, budget / stage);
   N2V2R_REQUIRE(a.S >= 2, "row lists: two stages of %zu bytes (X panel of %d x %d fp32 + the longest list, %d bytes) do not fit in shared memory", stage, W, l,
                 list_cap);
   const size_t smem = a.S * stage + 128;
-  const int grid = (int)((n + rb - 1) / rb);
-  int rpg = rows_per_group(rb);
-  if (g_rows_rpg >= rpg && g_rows_rpg <= 3) rpg = g_rows_rpg;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   int rc = mma_events_begin(s, &e0, &e1);
   if (rc) return rc;
@@ -410,6 +417,7 @@ using namespace n2v2r;
 
 extern "C" void n2v2r__debug_rows_rpg(int rpg) { g_rows_rpg = rpg; }
 extern "C" void n2v2r__debug_rows_parity(int on) { g_rows_parity = on; }
+extern "C" void n2v2r__debug_rows_two_per_sm(int on) { g_rows_two_per_sm = on; }
 
 extern "C" size_t n2v2r_rows_counts_bytes(int64_t n, int rows_per_block, int panel_cols) {
   if (n <= 0 || rows_per_block <= 0 || panel_cols <= 0) return 0;

@@ -78,11 +78,13 @@ def test_rows_round_trip(gpu, n, density, symmetric, rb, W):
 
 @pytest.mark.parametrize("n,density,l,rb,bits,W", [(1000, 0.03, 48, None, 24, None), (1500, 0.026, 64, 120, 16, None), (900, 0.05, 48, 300, 24, None),
                                                    (2100, 0.02, 32, 500, 1, None), (1024, 0.20, 48, 64, 24, None), (640, 0.08, 80, None, 24, None),
-                                                   (700, 0.04, 16, 9, 16, 64), (3000, 0.026, 48, 352, 24, 320), (1800, 0.03, 80, 528, 24, 128)])
+                                                   (700, 0.04, 16, 9, 16, 64), (3000, 0.026, 48, 352, 24, 320), (1800, 0.03, 80, 528, 24, 128),
+                                                   (3000, 0.026, 32, 16, 24, None), (2500, 0.03, 48, 12, 16, 128)])
 @pytest.mark.parametrize("symmetric", [True, False])
 def test_rows_product_against_float64(gpu, n, density, l, rb, bits, W, symmetric):
     """A x and A^T x of a row-list layer: within the fp32 accumulation bound of the float64 product, per entry; one, two and
-    three rows per lane group (rb up to 176 / 352 / 528), partial last block, panels that end inside the matrix."""
+    three rows per lane group (rb up to 176 / 352 / 528), partial last block, panels that end inside the matrix; the last two
+    cases have more row blocks than SMs and one row per group: two CTAs share an SM."""
     from node2vec2rank_b200 import device as D
     a = _sparse(n, density, 5 + n + l, symmetric, bits)
     x32 = torch.from_numpy(a).to(gpu)
