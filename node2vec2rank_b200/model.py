@@ -7,11 +7,11 @@ and exceptions.  `graphs` may be float32 ndarrays (what the reference's DataLoad
 device.DeviceLayer objects (DataLoader with "device_resident": true).
 
 Additive, optional config keys (defaults keep reference behaviour):
-  block_width (int, default: max dim + >=24 guard vectors rounded up to 16): solver block l
+  block_width (int, default: max dim + >=24 guard vectors rounded up to 16; + >=8 when every layer is held as row lists): solver block l
   solver_tol (float, default 1e-5), solver_max_iters (int, default 400)
   storage_planes (int | None): bf16 planes per weighted layer (None = exact)
-  layer_storage ("auto" | "planes" | "tiles", default "auto"): dense bf16 planes, or compressed tiles for sparse
-      layers (device.make_layer); "auto" picks tiles for large layers under 8 % density
+  layer_storage ("auto" | "rows" | "tiles" | "planes" | "e4m3", default "auto"): row lists of the fp32 non-zeros (large layers
+      under 4.5 % density), compressed tiles (up to 8 %), dense bf16 planes, one e4m3 plane (binarised) (device.make_layer)
   layer_sharded (bool, default False): under torch.distributed (one process per GPU) `graphs` holds only
       this rank's contiguous block of layers (dist.layer_partition); Y is all-reduced per operator
       application, embeddings are all-gathered, every rank returns the full tables
