@@ -33,6 +33,7 @@ namespace n2v2r {
 
 static int g_rows_rpg = 0;       // debug: force the rows per group (0 = heuristic)
 constexpr uint32_t kRowsPad = 0xFFFFFFFFu;   // column of the padding entry that completes the last 16-byte pair of an odd row
+static int g_rows_lanes8 = 1;       // debug: 0 = groups of 4 lanes also for l = 64; 2 = groups of 8 lanes also for l = 32
 static int g_rows_two_per_sm = 1;   // debug: 0 = never two CTAs per SM
 static int g_rows_parity = 1;    // debug: 0 = the builder writes every row's entries in plain column order
 
@@ -353,6 +354,143 @@ __global__ void __launch_bounds__(kRowsThreads, (RPG == 1 && L16 <= 3) ? 2 : 1) 
   }
 }
 
+// ---- the same product with groups of EIGHT lanes, for l = 64 (and, behind a debug switch, 32) -------------------------
+// A row of X is then one (l = 32) or two (l = 64) whole 128-byte wavefronts, read by one group alone: no pairing of groups
+// inside a wavefront, hence no half-empty wavefronts when the partner's row is shorter and no bank conflicts whatever the
+// columns are.  A warp holds 4 groups, a group owns RPG <= 4 consecutive rows (4 NCH accumulators per row and lane, lane t
+// holds columns 4 t .. 4 t + 3 of every 32-column chunk).  Same lists, same producer.
+template <int NCH, int RPG>     // NCH = l / 32
+__global__ void __launch_bounds__(kRowsThreads, 1) rows_product8_kernel(const RowsArgs a) {
+  extern __shared__ __align__(128) uint8_t smem_rows[];
+  __shared__ __align__(8) uint64_t bars[16];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t ring = (smem_u32(smem_rows) + 127u) & ~127u;
+  const uint32_t bar_full = smem_u32(&bars[0]), bar_empty = smem_u32(&bars[8]);
+  const uint32_t row_bytes = (uint32_t)a.l * 4u;
+  const uint32_t x_bytes = (uint32_t)a.W * row_bytes;
+  const uint32_t stage_bytes = x_bytes + (uint32_t)a.list_cap;
+  const int64_t row_base = (int64_t)blockIdx.x * a.rb;
+  const int rows_here = (int)max((int64_t)0, min((int64_t)a.rb, a.n - row_base));
+  const int n_groups = (rows_here + RPG - 1) / RPG;
+  const int n_cwarps = (n_groups + 3) >> 2;
+  const uint32_t hdr_bytes = (uint32_t)((2 * (a.rb + 1) + 15) & ~15);
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < a.S; ++i) { mbar_init(bar_full + 8 * i, 1); mbar_init(bar_empty + 8 * i, n_cwarps); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (warp == kRowsWarps) {
+    if (lane == 0 && n_cwarps > 0) {
+      int st = 0; uint32_t ph = 0;
+      const uint32_t* lp = a.list_ptr + (size_t)blockIdx.x * a.n_panels;
+      uint32_t q0 = __ldg(lp);
+      for (int p = 0; p < a.n_panels; ++p) {
+        const uint32_t q1 = __ldg(lp + p + 1);
+        mbar_wait(bar_empty + 8 * st, ph ^ 1u);
+        const uint32_t rows = (uint32_t)min((int64_t)a.W, a.n - (int64_t)p * a.W);
+        mbar_expect_tx(bar_full + 8 * st, rows * row_bytes + (q1 - q0) * 16u);
+        bulk_copy_g2s(ring + st * stage_bytes, a.x + (size_t)p * a.W * a.l, rows * row_bytes, bar_full + 8 * st);
+        bulk_copy_g2s(ring + st * stage_bytes + x_bytes, a.lists + q0, (q1 - q0) * 16u, bar_full + 8 * st);
+        q0 = q1;
+        if (++st == a.S) { st = 0; ph ^= 1u; }
+      }
+    }
+    return;
+  }
+  if (warp >= n_cwarps) return;
+  const int g = threadIdx.x >> 3, t = lane & 7;
+  const bool have = g < n_groups;
+  float acc[RPG][4 * NCH];
+#pragma unroll
+  for (int j = 0; j < RPG; ++j)
+#pragma unroll
+    for (int i = 0; i < 4 * NCH; ++i) acc[j][i] = 0.f;
+  int st = 0; uint32_t ph = 0;
+  for (int p = 0; p < a.n_panels; ++p) {
+    mbar_wait(bar_full + 8 * st, ph);
+    const uint32_t xbase = ring + st * stage_bytes + t * 16;
+    const uint32_t hdr = ring + st * stage_bytes + x_bytes;
+    const uint32_t ent = hdr + hdr_bytes;
+    uint32_t pp[RPG + 1];
+#pragma unroll
+    for (int j = 0; j <= RPG; ++j) pp[j] = have ? ld_shared_u16(hdr + 2u * (uint32_t)min(RPG * g + j, a.rb)) : 0u;
+#pragma unroll
+    for (int j = 0; j < RPG; ++j) {
+      for (uint32_t e = pp[j]; __any_sync(0xffffffffu, e < pp[j + 1]); ++e) {      // e counts 16-byte pairs of entries
+        if (e < pp[j + 1]) {
+          const uint4 q = ld_shared_v4(ent + 16u * e);
+          {
+            const float v = __uint_as_float(q.y);
+            const uint32_t ad = xbase + q.x * row_bytes;
+#pragma unroll
+            for (int s = 0; s < NCH; ++s) {
+              const float4 x = lds128f(ad + s * 128);
+              acc[j][4 * s + 0] = fmaf(v, x.x, acc[j][4 * s + 0]);
+              acc[j][4 * s + 1] = fmaf(v, x.y, acc[j][4 * s + 1]);
+              acc[j][4 * s + 2] = fmaf(v, x.z, acc[j][4 * s + 2]);
+              acc[j][4 * s + 3] = fmaf(v, x.w, acc[j][4 * s + 3]);
+            }
+          }
+          if (q.z != kRowsPad) {
+            const float v = __uint_as_float(q.w);
+            const uint32_t ad = xbase + q.z * row_bytes;
+#pragma unroll
+            for (int s = 0; s < NCH; ++s) {
+              const float4 x = lds128f(ad + s * 128);
+              acc[j][4 * s + 0] = fmaf(v, x.x, acc[j][4 * s + 0]);
+              acc[j][4 * s + 1] = fmaf(v, x.y, acc[j][4 * s + 1]);
+              acc[j][4 * s + 2] = fmaf(v, x.z, acc[j][4 * s + 2]);
+              acc[j][4 * s + 3] = fmaf(v, x.w, acc[j][4 * s + 3]);
+            }
+          }
+        }
+      }
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(bar_empty + 8 * st);
+    if (++st == a.S) { st = 0; ph ^= 1u; }
+  }
+#pragma unroll
+  for (int j = 0; j < RPG; ++j) {
+    const int r = RPG * g + j;
+    if (have && r < rows_here) {
+      float* dst = a.y + (size_t)(row_base + r) * a.l + 4 * t;
+#pragma unroll
+      for (int s = 0; s < NCH; ++s) {
+        float4 v = make_float4(acc[j][4 * s], acc[j][4 * s + 1], acc[j][4 * s + 2], acc[j][4 * s + 3]);
+        float* d = dst + 32 * s;
+        if (a.accumulate) {
+          const float4 o = *reinterpret_cast<const float4*>(d);
+          v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
+        }
+        *reinterpret_cast<float4*>(d) = v;
+      }
+    }
+  }
+}
+
+template <int NCH, int RPG>
+static int launch_rows8(cudaStream_t s, const RowsArgs& a, int grid, size_t smem) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    N2V2R_CUDA(cudaFuncSetAttribute(rows_product8_kernel<NCH, RPG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024 - 1024)));
+    attr_set = true;
+  }
+  rows_product8_kernel<NCH, RPG><<<grid, kRowsThreads, smem, s>>>(a);
+  N2V2R_CHECK_LAUNCH();
+  return N2V2R_OK;
+}
+
+template <int NCH>
+static int launch_rows8_r(cudaStream_t s, const RowsArgs& a, int grid, size_t smem, int rpg) {
+  switch (rpg) {
+    case 1: return launch_rows8<NCH, 1>(s, a, grid, smem);
+    case 2: return launch_rows8<NCH, 2>(s, a, grid, smem);
+    case 3: return launch_rows8<NCH, 3>(s, a, grid, smem);
+    default: return launch_rows8<NCH, 4>(s, a, grid, smem);
+  }
+}
+
 template <int L16, int RPG>
 static int launch_rows(cudaStream_t s, const RowsArgs& a, int grid, size_t smem) {
   static bool attr_set = false;
@@ -404,7 +542,12 @@ int stream_apply_rows(cudaStream_t s, int64_t n, int l, const uint32_t* list_ptr
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   int rc = mma_events_begin(s, &e0, &e1);
   if (rc) return rc;
-  if (rpg == 1) rc = launch_rows_l<1>(s, a, grid, smem);
+  const int rpg8 = (rb + 4 * kRowsWarps - 1) / (4 * kRowsWarps);       // rows per group of 8 lanes
+  // measured at C3: l = 64 0.783 ms against 0.821 ms with groups of 4 lanes; l = 32 0.503 against 0.463 ms (half as many entries
+  // per warp step: the loop overhead outweighs the full wavefronts), so only l = 64 takes it unless the debug switch says 2
+  if (g_rows_lanes8 && (l == 64 || (l == 32 && g_rows_lanes8 == 2)) && rpg8 <= 4 && !two_per_sm)
+    rc = l == 32 ? launch_rows8_r<1>(s, a, grid, smem, rpg8) : launch_rows8_r<2>(s, a, grid, smem, rpg8);
+  else if (rpg == 1) rc = launch_rows_l<1>(s, a, grid, smem);
   else if (rpg == 2) rc = launch_rows_l<2>(s, a, grid, smem);
   else rc = launch_rows_l<3>(s, a, grid, smem);
   if (rc) return rc;
@@ -418,6 +561,7 @@ using namespace n2v2r;
 extern "C" void n2v2r__debug_rows_rpg(int rpg) { g_rows_rpg = rpg; }
 extern "C" void n2v2r__debug_rows_parity(int on) { g_rows_parity = on; }
 extern "C" void n2v2r__debug_rows_two_per_sm(int on) { g_rows_two_per_sm = on; }
+extern "C" void n2v2r__debug_rows_lanes8(int on) { g_rows_lanes8 = on; }
 
 extern "C" size_t n2v2r_rows_counts_bytes(int64_t n, int rows_per_block, int panel_cols) {
   if (n <= 0 || rows_per_block <= 0 || panel_cols <= 0) return 0;

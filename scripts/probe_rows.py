@@ -31,6 +31,8 @@ del g
 out = {"n": n, "l": l, "keep": keep, "planes": layer_p.n_planes}
 del layer_p
 torch.cuda.synchronize()
+if "--lanes4" in sys.argv:
+    N.load().n2v2r__debug_rows_lanes8(ctypes.c_int(0))
 if "--one-per-sm" in sys.argv:
     N.load().n2v2r__debug_rows_two_per_sm(ctypes.c_int(0))
 if "--no-parity" in sys.argv:

@@ -79,12 +79,14 @@ def test_rows_round_trip(gpu, n, density, symmetric, rb, W):
 @pytest.mark.parametrize("n,density,l,rb,bits,W", [(1000, 0.03, 48, None, 24, None), (1500, 0.026, 64, 120, 16, None), (900, 0.05, 48, 300, 24, None),
                                                    (2100, 0.02, 32, 500, 1, None), (1024, 0.20, 48, 64, 24, None), (640, 0.08, 80, None, 24, None),
                                                    (700, 0.04, 16, 9, 16, 64), (3000, 0.026, 48, 352, 24, 320), (1800, 0.03, 80, 528, 24, 128),
-                                                   (3000, 0.026, 32, 16, 24, None), (2500, 0.03, 48, 12, 16, 128)])
+                                                   (3000, 0.026, 32, 16, 24, None), (2500, 0.03, 48, 12, 16, 128),
+                                                   (3000, 0.026, 32, 338, 24, None), (2000, 0.03, 64, 250, 24, 128), (1200, 0.05, 32, 40, 16, 64)])
 @pytest.mark.parametrize("symmetric", [True, False])
 def test_rows_product_against_float64(gpu, n, density, l, rb, bits, W, symmetric):
     """A x and A^T x of a row-list layer: within the fp32 accumulation bound of the float64 product, per entry; one, two and
     three rows per lane group (rb up to 176 / 352 / 528), partial last block, panels that end inside the matrix; the last two
-    cases have more row blocks than SMs and one row per group: two CTAs share an SM."""
+    cases before the last three have more row blocks than SMs and one row per group: two CTAs share an SM; l = 64 runs with
+    groups of 8 lanes (1 to 4 rows per group) when a block has at most 352 rows."""
     from node2vec2rank_b200 import device as D
     a = _sparse(n, density, 5 + n + l, symmetric, bits)
     x32 = torch.from_numpy(a).to(gpu)
@@ -105,6 +107,25 @@ def test_rows_product_against_float64(gpu, n, density, l, rb, bits, W, symmetric
     yp = D.layer_apply(D.make_layer(x32, storage="planes"), x)
     yr = D.layer_apply(L, x)
     assert float((yp - yr).abs().max() / yp.abs().max()) <= 5e-6
+
+
+def test_rows_groups_of_eight_lanes_at_l32(gpu):
+    """l = 32 with groups of 8 lanes (off by default: slower there; kept behind the debug switch): same product."""
+    import ctypes
+    from node2vec2rank_b200 import _native as N, device as D
+    a = _sparse(2600, 0.03, 17)
+    L = D.make_rows_layer(torch.from_numpy(a).to(gpu), rows_block=300, max_list_bytes=None)
+    x = torch.randn((2600, 32), device=gpu)
+    y4 = D.layer_apply(L, x)
+    N.load().n2v2r__debug_rows_lanes8(ctypes.c_int(2))
+    try:
+        y8 = D.layer_apply(L, x)
+    finally:
+        N.load().n2v2r__debug_rows_lanes8(ctypes.c_int(1))
+    ref = torch.from_numpy(a.astype(np.float64)).to(gpu) @ x.double()
+    scale = (torch.from_numpy(np.abs(a).astype(np.float64)).to(gpu) @ x.double().abs()).clamp_min(1e-30)
+    assert float(((y8.double() - ref).abs() / scale).max()) <= 4e-6
+    assert torch.equal(y4.view(torch.int32), y8.view(torch.int32))      # same entries in the same order per row: same bits
 
 
 def test_rows_solver_matches_planes_solver(gpu):
