@@ -490,7 +490,7 @@ def cpu_baseline_leg(w, n, T):
             "extrapolated_s": one_run * runs, "extrapolated_phases_s": parts}
 
 
-def build_workload_layers(w, n, layer_ids, want_f32=False, storage="auto", graph_seed=None):
+def build_workload_layers(w, n, layer_ids, want_f32=False, storage="auto", graph_seed=None, block_width=None):
     """Set-up of one workload (untimed in `value`): K0 generate + K1 load pass per layer, exactly what the timed step
     works on.  Returns (layers, fp32 device matrices or None per layer, [(event, event)] around every load pass).
     tests/test_gpu_bench_shapes.py runs the benchmark shapes in miniature through this function and hot_path()."""
@@ -503,7 +503,8 @@ def build_workload_layers(w, n, layer_ids, want_f32=False, storage="auto", graph
         raw = D.sbm_generate(n, w["K"], Bs[t], seed=seed, layer=t, weighted=w["weighted"])
         pa, pb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         pa.record()
-        layer, f32 = D.preprocess_to_layer(raw, top_percent_keep=w["keep"], binarize=w["binarize"], want_f32=want_f32, storage=storage)
+        layer, f32 = D.preprocess_to_layer(raw, top_percent_keep=w["keep"], binarize=w["binarize"], want_f32=want_f32, storage=storage,
+                                           block_width=block_width or D.default_block_width(max(DIMS), n, "rows"))
         pb.record()
         events.append((pa, pb))
         del raw
@@ -601,7 +602,8 @@ def run_b200_arm(args):
     t_setup = time.perf_counter()
     want_host = not args.no_e2e and slab_rows is None
     layers, f32s, pre_events = build_workload_layers(w, n, mine, want_f32=want_host or slab_rows is not None,
-                                                     storage="planes" if slab_rows is not None else args.layer_storage)
+                                                     storage="planes" if slab_rows is not None else args.layer_storage,
+                                                     block_width=l or None)
     if slab_rows is not None:                      # keep only this rank's rows of its layer (and their transpose)
         layers = [D.make_slab_layer(f, slab_rows.start, len(slab_rows), n_planes=L.n_planes) for f, L in zip(f32s, layers)]
     host_graphs = []

@@ -536,7 +536,8 @@ int stream_apply_rows(cudaStream_t s, int64_t n, int l, const uint32_t* list_ptr
   const bool two_per_sm = g_rows_two_per_sm && rpg == 1 && l <= 48 && grid > sm_count() && 2 * stage + 128 <= 112 * 1024;
   const size_t budget = two_per_sm ? (size_t)112 * 1024 - 128 : (size_t)227 * 1024 - 1024 - 256;
   a.S = (int)std::min<size_t>(8, budget / stage);
-  N2V2R_REQUIRE(a.S >= 2, "row lists: two stages of %zu bytes (X panel of %d x %d fp32 + the longest list, %d bytes) do not fit in shared memory", stage, W, l,
+  // a layer built for a narrower block (wider panels) still works as long as ONE stage fits: copy and compute then alternate
+  N2V2R_REQUIRE(a.S >= 1, "row lists: a stage of %zu bytes (X panel of %d x %d fp32 + the longest list, %d bytes) does not fit in shared memory", stage, W, l,
                 list_cap);
   const size_t smem = a.S * stage + 128;
   cudaEvent_t e0 = nullptr, e1 = nullptr;

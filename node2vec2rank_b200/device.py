@@ -407,8 +407,10 @@ def make_tiles_layer(x32: torch.Tensor, colsum=None, max_density=None, tile_rows
 
 ROWS_MAX_DENSITY = 0.045        # layers sparser than this are stored as row lists (storage="auto"): the fp32 FMA-pipe product costs
                                 # about 0.26 ms per percent of density at n = 50 000 against 0.96 ms for the tiles at any density
-ROWS_PANEL_COLS = 256           # columns per panel: the X panel (256 x l fp32) and the block's list make one stage in shared memory
-ROWS_MAX_LIST_BYTES = 36 * 1024  # longest (block, panel) list a layer may have: two stages must fit beside two X panels (l <= 80)
+ROWS_PANEL_COLS = 256           # columns per panel when the solver's block width is not known at build time: the X panel (256 x l
+                                # fp32) and the block's list make one stage in shared memory, and two stages fit for every l <= 80
+ROWS_MAX_LIST_BYTES = 36 * 1024  # longest (block, panel) list a layer may have then: two stages must fit beside two X panels
+ROWS_STAGE_BYTES = 113 * 1024   # half of the shared memory the product kernel can use: one stage = X panel + longest list
 ROWS_GROUPS = 176               # groups of 4 lanes per CTA of the product kernel (22 warps): rows per block <= 3 x this
 
 
@@ -424,6 +426,18 @@ def sm_count():
     return _SM_COUNT[dev]
 
 
+def rows_panel_cols(block_width):
+    """Columns per panel of a row-list layer built for a solver block of `block_width` columns: the widest panel (multiple of
+    64, at most 512) whose stage -- X panel + a list of about 80 bytes per column at C3's 2.6 % -- fits twice in shared memory.
+    Wider panels mean longer row segments per panel, i.e. fewer idle lane-group steps: a C3 pass at l = 32 takes 0.463 / 0.441 /
+    0.427 / 0.416 / 0.407 ms with 256 / 320 / 384 / 448 / 512 columns.  A layer built for a block width also works with wider
+    blocks as long as ONE stage fits (the kernel then runs without overlap of copy and compute)."""
+    if not block_width:
+        return ROWS_PANEL_COLS
+    w = ROWS_STAGE_BYTES // (4 * int(block_width) + 96)
+    return int(max(128, min(512, w // 64 * 64)))
+
+
 def rows_per_block(n):
     """Rows per block of a row-list layer: one block per SM when the groups can own that many rows (<= 3 each), else the
     smallest split into equal waves."""
@@ -434,9 +448,12 @@ def rows_per_block(n):
     return max(1, (n + sms * waves - 1) // (sms * waves))
 
 
-def make_rows_layer(x32: torch.Tensor, colsum=None, max_density=None, rows_block=None, panel_cols=None, max_list_bytes=ROWS_MAX_LIST_BYTES):
+def make_rows_layer(x32: torch.Tensor, colsum=None, max_density=None, rows_block=None, panel_cols=None, max_list_bytes=ROWS_MAX_LIST_BYTES,
+                    block_width=None):
     """fp32 (n, n) device matrix -> DeviceLayer(storage="rows"), or None when the matrix is denser than `max_density` or one
-    of its (block, panel) lists is longer than `max_list_bytes` (a hub row block: the caller picks another storage)."""
+    of its (block, panel) lists is longer than `max_list_bytes` (a hub row block: the caller picks another storage).
+    block_width: the solver block the layer will be multiplied with, when known: sets the panel width (rows_panel_cols) and
+    the list bound (what is left of a stage beside the X panel)."""
     lib = N.load()
     n = x32.shape[0]
     assert x32.dim() == 2 and x32.shape[0] == x32.shape[1] and x32.dtype == torch.float32, "layer must be a square float32 matrix"
@@ -444,7 +461,9 @@ def make_rows_layer(x32: torch.Tensor, colsum=None, max_density=None, rows_block
         x32 = x32.contiguous()
     dev = x32.device
     rb = int(rows_block) if rows_block else rows_per_block(n)
-    W = int(panel_cols) if panel_cols else ROWS_PANEL_COLS
+    W = int(panel_cols) if panel_cols else rows_panel_cols(block_width)
+    if block_width and not panel_cols and max_list_bytes == ROWS_MAX_LIST_BYTES:
+        max_list_bytes = ROWS_STAGE_BYTES - W * 4 * int(block_width)
     n_lists = ((n + rb - 1) // rb) * ((n + W - 1) // W)
 
     def build(src):
@@ -476,7 +495,7 @@ def make_rows_layer(x32: torch.Tensor, colsum=None, max_density=None, rows_block
                        n_units_t=0 if at is None else at[2], list_cap_t=0 if at is None else at[3], n_entries_t=0 if at is None else at[4])
 
 
-def make_layer(x32: torch.Tensor, n_planes=None, colsum=None, check_symmetry=True, storage="auto"):
+def make_layer(x32: torch.Tensor, n_planes=None, colsum=None, check_symmetry=True, storage="auto", block_width=None):
     """fp32 (n, n) device matrix -> DeviceLayer.  storage "auto" for n >= TILES_MIN_N: row lists when the density is <=
     ROWS_MAX_DENSITY (and no list is too long for a stage), compressed tiles when it is <= TILES_MAX_DENSITY, one e4m3 plane
     for binarised layers, else bf16 planes + symmetry flag / transposed copy.  "rows" / "tiles" / "planes" / "e4m3" force one."""
@@ -488,7 +507,7 @@ def make_layer(x32: torch.Tensor, n_planes=None, colsum=None, check_symmetry=Tru
         return make_layer(x32, n_planes=1, colsum=colsum, check_symmetry=check_symmetry, storage="planes").to_e4m3()
     if storage == "rows" or (storage == "auto" and n >= TILES_MIN_N and n_planes is None):
         layer = make_rows_layer(x32, colsum=colsum, max_density=None if storage == "rows" else ROWS_MAX_DENSITY,
-                                max_list_bytes=None if storage == "rows" else ROWS_MAX_LIST_BYTES)
+                                max_list_bytes=None if storage == "rows" else ROWS_MAX_LIST_BYTES, block_width=block_width)
         if layer is not None:
             return layer
         if storage == "rows":
@@ -549,7 +568,7 @@ def _staging(chunk_rows, cols):
     return _pack_staging[key]
 
 
-def layers_from_host(arrays, n_planes=None, transfer="auto", storage="auto"):
+def layers_from_host(arrays, n_planes=None, transfer="auto", storage="auto", block_width=None):
     """float32 (n, n) host matrices (what the reference's DataLoader hands to N2V2R) -> DeviceLayers.
 
     transfer = "dense": double-buffered H2D of the dense matrices (the copy of layer t+1 runs on a copy stream while
@@ -577,11 +596,11 @@ def layers_from_host(arrays, n_planes=None, transfer="auto", storage="auto"):
         except RuntimeError:                               # no lockable host memory for the staging slots: dense copies
             slots = None
         if slots is not None:
-            return _layers_from_host_packed(srcs, n_planes, chunk_rows, slots, storage)
-    return _layers_from_host_dense(srcs, n_planes, storage)
+            return _layers_from_host_packed(srcs, n_planes, chunk_rows, slots, storage, block_width)
+    return _layers_from_host_dense(srcs, n_planes, storage, block_width)
 
 
-def _layers_from_host_packed(srcs, n_planes, chunk_rows, slots, storage="auto"):
+def _layers_from_host_packed(srcs, n_planes, chunk_rows, slots, storage="auto", block_width=None):
     import queue
     import threading
     dev = _dev()
@@ -672,7 +691,7 @@ def _layers_from_host_packed(srcs, n_planes, chunk_rows, slots, storage="auto"):
             if isinstance(ev, BaseException):
                 raise ev
             cur.wait_event(ev)
-            layers.append(make_layer(dense[t % 2], n_planes=n_planes, storage=storage))
+            layers.append(make_layer(dense[t % 2], n_planes=n_planes, storage=storage, block_width=block_width))
             done = torch.cuda.Event()
             done.record(cur)
             consumed.put(done)
@@ -689,7 +708,7 @@ def _layers_from_host_packed(srcs, n_planes, chunk_rows, slots, storage="auto"):
     return layers
 
 
-def _layers_from_host_dense(srcs, n_planes, storage="auto"):
+def _layers_from_host_dense(srcs, n_planes, storage="auto", block_width=None):
     dev = _dev()
     t_begin = time.perf_counter()
     stats = dict(packed_chunks=0, dense_chunks=len(srcs), h2d_bytes=sum(x.numel() * 4 for x in srcs), total_s=0.0)
@@ -715,7 +734,7 @@ def _layers_from_host_dense(srcs, n_planes, storage="auto"):
         if t + 1 < len(srcs):
             issue(t + 1)
         cur.wait_event(copied[t])
-        layers.append(make_layer(bufs[t % 2], n_planes=n_planes, storage=storage))
+        layers.append(make_layer(bufs[t % 2], n_planes=n_planes, storage=storage, block_width=block_width))
         built[t].record(cur)
     cur.wait_stream(copy)
     stats["total_s"] = time.perf_counter() - t_begin        # host time: the last load pass may still be running
@@ -738,7 +757,7 @@ def finish_layer(planes, n, ld_p, P, colsum, check_symmetry=True, known_symmetri
 
 
 def preprocess_to_layer(x: torch.Tensor, threshold=None, top_percent_keep=100, binarize=False, absolute=False,
-                        project_unipartite_on="columns", storage_planes=None, want_f32=False, storage="auto"):
+                        project_unipartite_on="columns", storage_planes=None, want_f32=False, storage="auto", block_width=None):
     """network_transform (preprocessing_utils.py:116-141) on the device.
 
     Returns (DeviceLayer, out_f32 | None).  Order of operations as the reference: abs ->
@@ -772,10 +791,10 @@ def preprocess_to_layer(x: torch.Tensor, threshold=None, top_percent_keep=100, b
     if P == 0:
         # exact storage: materialise fp32 once, count the planes it needs, then split
         if cut is None and not binarize and not absolute and threshold is None:
-            layer = make_layer(x, check_symmetry=check_sym, storage=storage)   # identity transform: store the projected matrix directly
+            layer = make_layer(x, check_symmetry=check_sym, storage=storage, block_width=block_width)   # identity transform: store the projected matrix directly
             return layer, (x if want_f32 else None)
         out, _, _, cs = transform(x, absolute, threshold, cut, binarize, want_f32=True, want_colsum=True)
-        layer = make_layer(out, colsum=cs, check_symmetry=check_sym, storage=storage)
+        layer = make_layer(out, colsum=cs, check_symmetry=check_sym, storage=storage, block_width=block_width)
         return layer, (out if want_f32 else None)
     out, planes, ld_p, cs = transform(x, absolute, threshold, cut, binarize, want_f32=want_f32, n_planes=P,
                                       want_colsum=True)

@@ -101,10 +101,13 @@ class N2V2R:
             host = [None if isinstance(g, D.DeviceLayer) else np.asarray(g) for g in self.graphs]
             arrays = [a for a in host if a is not None]
             planes = self.config.get("storage_planes")
+            # the block the solve will use if the layers end up as row lists: sizes their panels (device.rows_panel_cols)
+            n_hint = arrays[0].shape[0] if arrays else 0
+            l_hint = int(self.config.get("block_width") or D.default_block_width(self.max_embed_dim, max(n_hint, 1), "rows"))
             if arrays and all(a.dtype == np.float32 and a.ndim == 2 and a.shape == arrays[0].shape for a in arrays):
                 # H2D of layer t+1 overlaps the load pass of layer t; large sparse layers cross PCIe packed (K0c)
                 built = iter(D.layers_from_host(arrays, n_planes=planes, transfer=self.config.get("host_transfer", "auto"),
-                                                storage=self.config.get("layer_storage", "auto")))
+                                                storage=self.config.get("layer_storage", "auto"), block_width=l_hint))
                 self.transfer_stats = D.layers_from_host.last_stats
                 self._layers = [g if a is None else next(built) for g, a in zip(self.graphs, host)]
                 return self._layers
@@ -116,7 +119,7 @@ class N2V2R:
                     x = D.to_device(a)
                     if x.dtype != torch.float32:        # the reference hands fp32 to the SVD (preprocessing_utils.py:141)
                         x = x.to(torch.float32)
-                    layers.append(D.make_layer(x, n_planes=planes, storage=self.config.get("layer_storage", "auto")))
+                    layers.append(D.make_layer(x, n_planes=planes, storage=self.config.get("layer_storage", "auto"), block_width=l_hint))
             self._layers = layers
         return self._layers
 

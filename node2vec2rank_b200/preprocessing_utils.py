@@ -27,12 +27,13 @@ def bipartite_to_unipartite_projection(graph, project_unipartite_on="columns"):
 
 
 def network_transform_device(network, threshold=None, top_percent_keep=100, binarize=False, absolute=False,
-                             project_unipartite_on="columns", storage_planes=None, want_f32=False, storage="auto"):
-    """Device-resident variant: returns (DeviceLayer, fp32 device tensor | None)."""
+                             project_unipartite_on="columns", storage_planes=None, want_f32=False, storage="auto", block_width=None):
+    """Device-resident variant: returns (DeviceLayer, fp32 device tensor | None).  block_width: the solver block the layer
+    will be multiplied with, when known (sizes the panels of a row-list layer, device.rows_panel_cols)."""
     x = D.to_device(network)
     return D.preprocess_to_layer(x, threshold=threshold, top_percent_keep=top_percent_keep, binarize=binarize,
                                  absolute=absolute, project_unipartite_on=project_unipartite_on,
-                                 storage_planes=storage_planes, want_f32=want_f32, storage=storage)
+                                 storage_planes=storage_planes, want_f32=want_f32, storage=storage, block_width=block_width)
 
 
 def network_transform(network, threshold=None, top_percent_keep=100, binarize=False, absolute=False,

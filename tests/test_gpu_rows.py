@@ -156,14 +156,37 @@ def test_rows_solver_matches_planes_solver(gpu):
 
 
 def test_rows_stage_that_does_not_fit_fails_loudly(gpu):
-    """528 rows per block x 256 columns at 3 % and l = 80: two stages (X panel + longest list) exceed shared memory."""
+    """528 rows per block x 512 columns at 3 % and l = 80: not even one stage (X panel + longest list) fits in shared memory."""
     from node2vec2rank_b200 import device as D
     from node2vec2rank_b200._native import NativeError
     a = torch.from_numpy(_sparse(1800, 0.03, 3)).to(gpu)
-    L = D.make_rows_layer(a, rows_block=528, panel_cols=256, max_list_bytes=None)
-    with pytest.raises(NativeError, match="do not fit in shared memory"):
+    L = D.make_rows_layer(a, rows_block=528, panel_cols=512, max_list_bytes=None)
+    with pytest.raises(NativeError, match="does not fit in shared memory"):
         D.layer_apply(L, torch.zeros((1800, 80), device=gpu))
     assert D.make_rows_layer(a, rows_block=528, panel_cols=256, max_list_bytes=16 * 1024) is None      # what storage="auto" does
+
+
+def test_rows_layer_built_for_a_block_width(gpu):
+    """A layer built for the solver's block width gets the widest panels whose stage fits twice (512 columns for l = 32); it still
+    multiplies wider blocks, with one stage (no overlap of copy and compute) when two no longer fit."""
+    from node2vec2rank_b200 import device as D
+    assert [D.rows_panel_cols(l) for l in (None, 16, 32, 48, 64, 80)] == [256, 512, 512, 384, 320, 256]
+    n = 3000
+    a = _sparse(n, 0.026, 23)
+    x32 = torch.from_numpy(a).to(gpu)
+    L = D.make_layer(x32, storage="rows", block_width=32)
+    assert L.storage == "rows" and L.panel_cols == 512
+    a64 = torch.from_numpy(a.astype(np.float64)).to(gpu)
+    for l in (32, 48, 80):
+        x = torch.randn((n, l), device=gpu)
+        y = D.layer_apply(L, x)
+        ref = a64 @ x.double()
+        scale = (a64.abs() @ x.double().abs()).clamp_min(1e-30)
+        assert float(((y.double() - ref).abs() / scale).max()) <= 4e-6, l
+    # the solve on such layers
+    emb, sigma, _, info = D.uase([L], 8, l=32, seed=3, check_dims=[8])
+    emb2, sigma2, _, _ = D.uase([D.make_layer(x32, storage="planes")], 8, l=48, seed=4, check_dims=[8])
+    assert np.allclose(sigma, sigma2, rtol=2e-5)
 
 
 def test_auto_storage_picks_rows_then_tiles_then_planes(gpu, monkeypatch):
