@@ -606,28 +606,16 @@ def run_b200_arm(args):
                                                      block_width=l or None)
     if slab_rows is not None:                      # keep only this rank's rows of its layer (and their transpose)
         layers = [D.make_slab_layer(f, slab_rows.start, len(slab_rows), n_planes=L.n_planes) for f, L in zip(f32s, layers)]
+    host_graphs = []
+    for f32 in f32s:
+        if f32 is not None and want_host:  # what the reference's DataLoader hands to N2V2R: float32 (n, n) on the HOST (pinned)
+            h = torch.empty((n, n), dtype=torch.float32, pin_memory=True)
+            h.copy_(f32)
+            host_graphs.append(h.numpy())
+    del f32s
+    torch.cuda.synchronize()
     n_planes = layers[0].n_planes if layers else 0
     storage = layers[0].storage if layers else "planes"
-    host_graphs = []
-
-    def make_host_graphs():
-        """What the reference's DataLoader hands to N2V2R: float32 (n, n) on the HOST (pinned) -- the e2e leg's input."""
-        for f32 in f32s:
-            if f32 is not None and want_host:
-                h = torch.empty((n, n), dtype=torch.float32, pin_memory=True)
-                h.copy_(f32)
-                host_graphs.append(h.numpy())
-        f32s.clear()
-        torch.cuda.synchronize()
-
-    # Sparse storages leave room to keep the fp32 layers on the device through the timed steps, so the 80 GB of pinned host
-    # memory of the e2e leg are allocated AFTER them: locking that much memory makes the host reclaim page cache (code pages of
-    # the libraries included), and timed steps that ran right after it were seen to stall for 0.1 - 0.8 s on page faults.
-    defer_host = want_host and storage in ("rows", "tiles")
-    f32s = list(f32s)
-    if not defer_host:
-        make_host_graphs()
-    torch.cuda.synchronize()
     if not l:                                      # default block width: by the layers' storage (the same on every rank)
         l = D.default_block_width(max(DIMS), n, storage)
     setup_s = time.perf_counter() - t_setup
@@ -685,9 +673,6 @@ def run_b200_arm(args):
     if not args.no_e2e and slab_rows is None:
         del layers, scores, bordas
         torch.cuda.empty_cache()
-        if defer_host:
-            make_host_graphs()
-            torch.cuda.empty_cache()
         cfg = dict(embed_dimensions=DIMS, distance_metrics=METRICS, comp_strategy=w["strategy"], seed=SOLVER_SEED,
                    save_dir=None, verbose=-1, block_width=l, layer_sharded=world > 1, host_transfer=args.host_transfer,
                    layer_storage=args.layer_storage)
