@@ -17,6 +17,16 @@ def test_column_specs_order_and_skip():
         D.column_specs([2], ["manhattan"])
 
 
+def test_rows_panel_cols():
+    """Panel width of a row-list layer by the solver block it is built for: the widest multiple of 64 (<= 512) whose stage
+    (X panel + about 96 bytes of list per column) fits twice in the shared memory the product kernel can use."""
+    from node2vec2rank_b200 import device as D
+    assert [D.rows_panel_cols(l) for l in (None, 0, 16, 32, 48, 64, 80)] == [256, 256, 512, 512, 384, 320, 256]
+    for l in (16, 32, 48, 64, 80):
+        W = D.rows_panel_cols(l)
+        assert W % 64 == 0 and 2 * W * (4 * l + 96) <= 2 * D.ROWS_STAGE_BYTES
+
+
 def test_default_block_width():
     from node2vec2rank_b200 import device as D
     assert D.default_block_width(24, 50000) == 48
