@@ -86,8 +86,11 @@ class DataLoader():
             if callable(g):
                 g = g()
             if cfg.get("device_resident", False):
+                from . import device as D
+                dims = cfg.get("embed_dimensions") or []
+                hint = cfg.get("block_width") or (D.default_block_width(max(dims), g.shape[1], "rows") if len(dims) else None)
                 self.graphs.append(network_transform_device(g, storage_planes=cfg.get("storage_planes"),
-                                                            storage=cfg.get("layer_storage", "auto"), **kwargs)[0])
+                                                            storage=cfg.get("layer_storage", "auto"), block_width=hint, **kwargs)[0])
             else:
                 self.graphs.append(network_transform(g, **kwargs))
             del g
